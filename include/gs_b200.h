@@ -1,0 +1,144 @@
+/*
+ * gs_b200.h -- C ABI of the B200 (sm_100a) Gaussian-splatting rasteriser.
+ *
+ * One entry point per stage of the reference operator
+ * GaussianPointCloudRasterisation (reference file
+ * taichi_3d_gaussian_splatting/GaussianPointCloudRasterisation.py, "R.py" below).
+ * Every pointer is a raw CUDA device pointer unless it says "host"; sizes are
+ * element counts; `stream` is a cudaStream_t passed as void*.  No torch types.
+ * All functions return 0 on success, a negative GS_E_* code for bad arguments or
+ * capacity problems, or a positive cudaError_t from the launch.  The caller owns
+ * every buffer (the Python host allocates them through torch's caching allocator).
+ *
+ * Arithmetic: the forward entry points (inverse_pose .. blend_fwd) follow the
+ * "literal fp32" profile documented in DESIGN.md (no FMA contraction, IEEE / and
+ * sqrt, gs_expf polynomial) and are bit-exact with oracle/gs_oracle.c; the
+ * backward entry points use fast fp32 (FMA, ex2.approx) and are compared at
+ * 1e-4 relative.
+ */
+#ifndef GS_B200_H
+#define GS_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GS_OK 0
+#define GS_E_INVALID (-1)   /* bad argument (null pointer, W or H not a multiple of 16, ...) */
+#define GS_E_CAPACITY (-2)  /* a count exceeds what the int32 index contract allows */
+
+#define GS_TILE 16          /* R.py:27-28 */
+#define GS_BOUNDARY_TILES 3 /* R.py:26 */
+#define GS_FEATURES 56      /* R.py:208-236 */
+#define GS_RECORD_FLOATS 12 /* packed per-splat record: u v a b c rescale alpha r g b z pad */
+#define GS_GRAD_SLOTS 12    /* per-splat reduced gradients, see gs_blend_bwd */
+
+/* ABI / build identification.  Returns e.g. 100 for the first ABI revision. */
+int gs_abi_version(void);
+/* Human-readable text for a status returned by any entry point (static storage). */
+const char *gs_status_string(int status);
+
+/* Bytes of scratch `workspace` the forward needs for n points / k_capacity keys. */
+int64_t gs_project_workspace_bytes(int64_t n);
+int64_t gs_sort_workspace_bytes(int64_t k);
+
+/*
+ * Pose inverse.  Replaces inverse_SE3_qt_torch (reference utils.py:426-432, used R.py:845).
+ * q_pc_cam [n_obj,4] xyzw, t_pc_cam [n_obj,3] -> q_cam_pc, t_cam_pc.
+ */
+int gs_inverse_pose(const float *q_pc_cam, const float *t_pc_cam, int n_obj, float *q_cam_pc,
+                    float *t_cam_pc, void *stream);
+
+/*
+ * Cull + ordered compaction + projection + SH colour + tile count + offset scan in one pass.
+ * Replaces filter_point_in_camera (R.py:31-78), the mask compaction (R.py:861-865),
+ * generate_point_attributes_in_camera_plane (R.py:239-315, including the in-place
+ * quaternion normalisation of `features`), generate_num_overlap_tiles (R.py:106-128)
+ * and the cumsum/cat (R.py:913-922).
+ *
+ * Outputs are in ascending point-id order (decoupled look-back scan), each array
+ * sized for n entries; only the first M are written.
+ *   ids [n] i32, point_uv [n,2], point_in_camera [n,3], conic [n,4], alpha [n],
+ *   color [n,3], radii [n], num_tiles [n] i32, tile_offsets [n] i64 (exclusive scan),
+ *   records [n,12] (packed copy for the blend kernels), bbox [n,4] u16 (tu0,tu1,tv0,tv1),
+ *   depth_key [n] i32, totals [2] i64 = {M, K}.
+ * workspace: gs_project_workspace_bytes(n) bytes, contents irrelevant on entry.
+ */
+int gs_project_cull_sh(const float *xyz, float *features, const int8_t *invalid_mask,
+                       const int32_t *object_id, int64_t n, const float *intrinsics /*3x3*/,
+                       const float *q_cam_pc, const float *t_cam_pc, int n_obj,
+                       float near_plane, float far_plane, int width, int height,
+                       float depth_to_sort_key_scale,
+                       int32_t *ids, float *point_uv, float *point_in_camera, float *conic,
+                       float *alpha, float *color, float *radii, int32_t *num_tiles,
+                       int64_t *tile_offsets, float *records, uint16_t *bbox,
+                       int32_t *depth_key, int64_t *totals, void *workspace, void *stream);
+
+/*
+ * Key/payload emission.  Replaces generate_point_sort_key_by_num_overlap_tiles (R.py:131-172).
+ * keys [k] i64 = depth_key + (tile_id << 32), payload [k] i32 = offset in the visible list.
+ */
+int gs_emit_keys(const uint16_t *bbox, const int32_t *depth_key, const int64_t *tile_offsets,
+                 int64_t m, int64_t k, int width, int64_t *keys, int32_t *payload, void *stream);
+
+/*
+ * Stable ascending sort of (key, payload) pairs.  Replaces Tensor.sort() + gather (R.py:947-950).
+ * Only the significant bits are sorted: `depth_bits` low bits and `tile_bits` bits from bit 32
+ * (pass depth_bits = 32, tile_bits = 32 for a full signed 64-bit sort).  keys_alt/payload_alt
+ * are same-sized ping-pong buffers.  *result_in_alt (host int) tells where the result is.
+ */
+int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *payload_alt,
+                  int64_t k, int depth_bits, int tile_bits, void *workspace,
+                  int *result_in_alt /*host*/, void *stream);
+
+/*
+ * Tile ranges.  Replaces find_tile_start_and_end (R.py:175-193).  start/end [num_tiles] i32
+ * are zeroed by this call (R.py:954-957) and then filled.
+ */
+int gs_tile_ranges(const int64_t *sorted_keys, int64_t k, int32_t *tile_start, int32_t *tile_end,
+                   int num_tiles, void *stream);
+
+/*
+ * Forward blend.  Replaces gaussian_point_rasterisation (R.py:318-485).
+ * image [H,W,3], depth [H,W], acc_alpha [H,W], last_effective [H,W] i32, valid_count [H,W] i32.
+ * Every pixel is written (empty tiles give zeros).  With rgb_only != 0 only image is written.
+ */
+int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
+                 const int32_t *sorted_payload, const float *records, float *image, float *depth,
+                 float *acc_alpha, int32_t *last_effective, int32_t *valid_count, int rgb_only,
+                 void *stream);
+
+/*
+ * Backward blend.  Replaces loop 1 of gaussian_point_rasterisation_backward (R.py:531-705).
+ * splat_grads [m, 12] f32 must be zero on entry; per visible point it receives
+ *   0:duv.u 1:duv.v 2:dcov00 3:dcov01 4:dcov11 5:dr 6:dg 7:db 8:dlogit 9:|duv| 10:#pixels(as float) 11:0
+ * map_on_image [H,W,2] gets the per-pixel sum of |duv| (R.py:700-704).
+ */
+int gs_blend_bwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
+                 const int32_t *sorted_payload, const float *records, const float *image_grad,
+                 const float *acc_alpha, const int32_t *last_effective, float *splat_grads,
+                 float *map_on_image, void *stream);
+
+/*
+ * Per-point chain rule + SH band mask + factor scaling.  Replaces loop 2 of the backward kernel
+ * (R.py:707-772), _clear_grad_by_color_max_sh_band (R.py:1167-1182) and the factor multiplies
+ * (R.py:1105-1125).  grad_xyz [n,3] and grad_features [n,56] must be zero on entry; rows of the
+ * m visible points are stored.  Optional hook outputs (may be null), all [m,...] in list order:
+ * hook_grad_xyz [m,3], hook_grad_features [m,56], hook_grad_viewspace [m,2], hook_magnitude [m],
+ * hook_num_affected [m] i32 (R.py:1127-1142).
+ */
+int gs_point_bwd(const float *xyz, const float *features, const int32_t *object_id,
+                 const float *intrinsics, const float *q_cam_pc, const float *t_cam_pc,
+                 const float *t_pc_cam, int n_obj, const int32_t *ids, int64_t m,
+                 const float *point_in_camera, const float *splat_grads, int color_max_sh_band,
+                 float q_factor, float s_factor, float alpha_factor, float color_factor,
+                 float high_order_color_factor, float *grad_xyz, float *grad_features,
+                 float *hook_grad_xyz, float *hook_grad_features, float *hook_grad_viewspace,
+                 float *hook_magnitude, int32_t *hook_num_affected, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GS_B200_H */

@@ -1,0 +1,417 @@
+"""Drop-in for the reference operator `GaussianPointCloudRasterisation`.
+
+Same module / nested dataclasses / `torch.autograd.Function` forward and backward
+signatures as the reference (taichi_3d_gaussian_splatting/GaussianPointCloudRasterisation.py
+:775-1204, "R.py" below); the body of forward/backward launches the hand-written sm_100a
+kernels of libgs_b200.so through the C ABI of include/gs_b200.h.  No Taichi, no Triton, no
+CPU fallback: without the library this module does not import.
+
+Host-side differences from the reference, none of which change results:
+  * one host sync per forward (read M and K) instead of two (R.py:864, :916-931);
+  * per-point intermediates live in one buffer sized for N points (only the first M rows
+    are meaningful) instead of M-sized tensors allocated after a sync;
+  * empty frustum / empty key list returns zero images instead of uninitialised memory
+    (R.py:967-980).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+from typing import Callable, Dict, Optional
+
+import torch
+
+from . import _capi
+from .Camera import CameraInfo
+
+try:  # the reference derives its config from dataclass_wizard.YAMLWizard (R.py:20,777)
+    from dataclass_wizard import YAMLWizard
+except Exception:  # pragma: no cover - dataclass_wizard is optional here
+    class YAMLWizard:  # type: ignore
+        pass
+
+BOUNDARY_TILES = 3  # R.py:26
+TILE_WIDTH = 16     # R.py:27
+TILE_HEIGHT = 16    # R.py:28
+
+_lib = _capi.lib
+_REC = 12
+_GRAD_SLOTS = 12
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _align(x: int, a: int = 256) -> int:
+    return (x + a - 1) // a * a
+
+
+class _PointBuffers:
+    """Carves the per-visible-point arrays (capacity n rows) out of one byte buffer."""
+
+    FIELDS = (  # name, dtype, columns
+        ("ids", torch.int32, 1),
+        ("point_uv", torch.float32, 2),
+        ("point_in_camera", torch.float32, 3),
+        ("conic", torch.float32, 4),
+        ("alpha", torch.float32, 1),
+        ("color", torch.float32, 3),
+        ("radii", torch.float32, 1),
+        ("num_tiles", torch.int32, 1),
+        ("tile_offsets", torch.int64, 1),
+        ("records", torch.float32, _REC),
+        ("bbox", torch.int16, 4),
+        ("depth_key", torch.int32, 1),
+    )
+
+    def __init__(self, n: int, device: torch.device):
+        self.n = n
+        self.offsets: Dict[str, int] = {}
+        off = 0
+        for name, dtype, cols in self.FIELDS:
+            self.offsets[name] = off
+            off = _align(off + max(n, 1) * cols * torch.empty((), dtype=dtype).element_size())
+        self.storage = torch.empty(off, dtype=torch.uint8, device=device)
+        self.base = self.storage.data_ptr()
+
+    def ptr(self, name: str) -> int:
+        return self.base + self.offsets[name]
+
+    def view(self, name: str, rows: int) -> torch.Tensor:
+        for fname, dtype, cols in self.FIELDS:
+            if fname == name:
+                nbytes = rows * cols * torch.empty((), dtype=dtype).element_size()
+                off = self.offsets[name]
+                t = self.storage[off:off + nbytes].view(dtype)
+                return t.view(rows, cols) if cols > 1 else t
+        raise KeyError(name)
+
+
+def sort_key_bits(near_plane: float, far_plane: float, depth_to_sort_key_scale: float,
+                  num_tiles: int):
+    """How many low bits the depth part and how many bits the tile part of a key need.
+
+    depth key = i32(z * scale) with near < z < far (R.py:72-73,159-160).  A negative near plane
+    (negative depth keys) or a depth that does not fit 31 bits selects the full signed 64-bit sort.
+    """
+    max_depth = far_plane * depth_to_sort_key_scale * 1.001 + 2.0
+    if near_plane < 0.0 or not (max_depth < 2.0 ** 31):
+        return 32, 32
+    depth_bits = max(1, int(max_depth).bit_length())
+    tile_bits = max(1, (max(num_tiles, 1) - 1).bit_length())
+    return depth_bits, tile_bits
+
+
+def find_tile_start_and_end(point_in_camera_sort_key: torch.Tensor,
+                            tile_points_start: torch.Tensor,
+                            tile_points_end: torch.Tensor) -> None:
+    """Same call as the reference kernel of that name (R.py:175-193) on CUDA tensors."""
+    assert point_in_camera_sort_key.dtype == torch.int64 and point_in_camera_sort_key.is_cuda
+    assert tile_points_start.dtype == torch.int32 and tile_points_end.dtype == torch.int32
+    stream = torch.cuda.current_stream(point_in_camera_sort_key.device).cuda_stream
+    _capi.check(_lib.gs_tile_ranges(point_in_camera_sort_key.data_ptr(),
+                                    point_in_camera_sort_key.shape[0],
+                                    tile_points_start.data_ptr(), tile_points_end.data_ptr(),
+                                    tile_points_start.shape[0], stream), "gs_tile_ranges")
+
+
+class GaussianPointCloudRasterisation(torch.nn.Module):
+    @dataclass
+    class GaussianPointCloudRasterisationConfig(YAMLWizard):
+        near_plane: float = 0.8
+        far_plane: float = 1000.
+        depth_to_sort_key_scale: float = 100.
+        rgb_only: bool = False
+        # un-annotated, i.e. class constants, exactly like R.py:782-786
+        grad_color_factor = 5.
+        grad_high_order_color_factor = 1.
+        grad_s_factor = 0.5
+        grad_q_factor = 1.
+        grad_alpha_factor = 20.
+
+    @dataclass
+    class GaussianPointCloudRasterisationInput:
+        point_cloud: torch.Tensor  # Nx3
+        point_cloud_features: torch.Tensor  # Nx56
+        point_object_id: torch.Tensor  # N int32
+        point_invalid_mask: torch.Tensor  # N int8
+        camera_info: CameraInfo
+        q_pointcloud_camera: torch.Tensor  # Kx4 xyzw
+        t_pointcloud_camera: torch.Tensor  # Kx3
+        color_max_sh_band: int = 2
+
+    @dataclass
+    class BackwardValidPointHookInput:
+        point_id_in_camera_list: torch.Tensor  # M
+        grad_point_in_camera: torch.Tensor  # Mx3
+        grad_pointfeatures_in_camera: torch.Tensor  # Mx56
+        grad_viewspace: torch.Tensor  # Mx2
+        magnitude_grad_viewspace: torch.Tensor  # M
+        magnitude_grad_viewspace_on_image: torch.Tensor  # HxWx2
+        num_overlap_tiles: torch.Tensor  # M
+        num_affected_pixels: torch.Tensor  # M
+        point_depth: torch.Tensor  # M
+        point_uv_in_camera: torch.Tensor  # Mx2
+
+    def __init__(
+        self,
+        config: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig",
+        backward_valid_point_hook: Optional[Callable[["GaussianPointCloudRasterisation.BackwardValidPointHookInput"], None]] = None,
+    ):
+        super().__init__()
+        self.config = config
+        self.last_forward_info: Dict[str, object] = {}
+        outer = self
+
+        class _module_function(torch.autograd.Function):
+
+            @staticmethod
+            def forward(ctx,
+                        pointcloud,
+                        pointcloud_features,
+                        point_invalid_mask,
+                        point_object_id,
+                        q_pointcloud_camera,
+                        t_pointcloud_camera,
+                        camera_info,
+                        color_max_sh_band,
+                        ):
+                cfg = outer.config
+                out = _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask,
+                                    point_object_id, q_pointcloud_camera, t_pointcloud_camera,
+                                    camera_info)
+                outer.last_forward_info = out.info
+                ctx.set_materialize_grads(False)
+                ctx.camera_info = camera_info
+                ctx.color_max_sh_band = color_max_sh_band
+                # the outputs must not be reachable from ctx (output -> grad_fn -> ctx cycle)
+                image, depth, count = out.image, out.depth, out.count
+                out.image = out.depth = out.count = None
+                ctx.state = out
+                ctx.save_for_backward(pointcloud, pointcloud_features, point_object_id,
+                                      q_pointcloud_camera, t_pointcloud_camera)
+                return image, depth, count
+
+            @staticmethod
+            def backward(ctx, grad_rasterized_image, grad_rasterized_depth=None,
+                         grad_pixel_valid_point_count=None):
+                grad_pointcloud = grad_pointcloud_features = None
+                if ctx.needs_input_grad[0] or ctx.needs_input_grad[1]:
+                    pointcloud, pointcloud_features, point_object_id, _, t_pointcloud_camera = \
+                        ctx.saved_tensors
+                    grad_pointcloud, grad_pointcloud_features = _backward_impl(
+                        outer.config, ctx.state, pointcloud, pointcloud_features, point_object_id,
+                        t_pointcloud_camera, ctx.camera_info, ctx.color_max_sh_band,
+                        grad_rasterized_image, backward_valid_point_hook,
+                        GaussianPointCloudRasterisation.BackwardValidPointHookInput)
+                return grad_pointcloud, grad_pointcloud_features, None, None, None, None, None, None
+
+        self._module_function = _module_function
+
+    def forward(self, input_data: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput"):
+        camera_info = input_data.camera_info
+        assert camera_info.camera_width % TILE_WIDTH == 0
+        assert camera_info.camera_height % TILE_HEIGHT == 0
+        return self._module_function.apply(
+            input_data.point_cloud,
+            input_data.point_cloud_features,
+            input_data.point_invalid_mask,
+            input_data.point_object_id,
+            input_data.q_pointcloud_camera,
+            input_data.t_pointcloud_camera,
+            camera_info,
+            input_data.color_max_sh_band,
+        )
+
+
+class _ForwardState:
+    """Everything the backward needs, plus handles a test can read every stage from."""
+    __slots__ = ("n", "m", "k", "width", "height", "buffers", "payload", "keys", "tile_start",
+                 "tile_end", "image", "depth", "count", "acc_alpha", "last", "q_cam", "t_cam",
+                 "intrinsics", "info", "unsorted_keys", "unsorted_payload")
+
+
+def _check_inputs(pointcloud, features, invalid_mask, object_id, q, t, intrinsics):
+    if not pointcloud.is_cuda:
+        raise _capi.GsError("GaussianPointCloudRasterisation needs CUDA tensors (no CPU path exists)")
+    n = pointcloud.shape[0]
+    if pointcloud.dtype != torch.float32 or pointcloud.dim() != 2 or pointcloud.shape[1] != 3:
+        raise ValueError("point_cloud must be float32 [N,3]")
+    if features.dtype != torch.float32 or features.shape != (n, 56):
+        raise ValueError("point_cloud_features must be float32 [N,56]")
+    if not features.is_contiguous():
+        raise ValueError("point_cloud_features must be contiguous (it is normalised in place)")
+    if invalid_mask.dtype != torch.int8 or invalid_mask.shape[0] != n:
+        raise ValueError("point_invalid_mask must be int8 [N]")
+    if object_id.dtype != torch.int32 or object_id.shape[0] != n:
+        raise ValueError("point_object_id must be int32 [N]")
+    if q.dim() != 2 or q.shape[1] != 4 or t.dim() != 2 or t.shape[1] != 3 or q.shape[0] != t.shape[0]:
+        raise ValueError("q_pointcloud_camera must be [K,4] and t_pointcloud_camera [K,3]")
+    if tuple(intrinsics.shape) != (3, 3):
+        raise ValueError("camera_intrinsics must be 3x3")
+
+
+def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
+                  q_pointcloud_camera, t_pointcloud_camera, camera_info,
+                  keep_unsorted: bool = False) -> _ForwardState:
+    dev = pointcloud.device
+    intrinsics = camera_info.camera_intrinsics
+    _check_inputs(pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
+                  q_pointcloud_camera, t_pointcloud_camera, intrinsics)
+    W, H = int(camera_info.camera_width), int(camera_info.camera_height)
+    if W % TILE_WIDTH or H % TILE_HEIGHT:
+        raise ValueError("camera width and height must be multiples of 16")
+    n = pointcloud.shape[0]
+    n_obj = q_pointcloud_camera.shape[0]
+    xyz = pointcloud.detach().contiguous()
+    feat = pointcloud_features.detach()
+    inv = point_invalid_mask.contiguous()
+    oid = point_object_id.contiguous()
+    Kmat = intrinsics.detach().to(device=dev, dtype=torch.float32).contiguous()
+    q_pc = q_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
+    t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
+    stream = torch.cuda.current_stream(dev).cuda_stream
+
+    st = _ForwardState()
+    st.n, st.width, st.height, st.intrinsics = n, W, H, Kmat
+    st.unsorted_keys = st.unsorted_payload = None
+    st.q_cam = torch.empty_like(q_pc)
+    st.t_cam = torch.empty_like(t_pc)
+    _capi.check(_lib.gs_inverse_pose(q_pc.data_ptr(), t_pc.data_ptr(), n_obj, st.q_cam.data_ptr(),
+                                     st.t_cam.data_ptr(), stream), "gs_inverse_pose")
+
+    buf = _PointBuffers(n, dev)
+    st.buffers = buf
+    totals = torch.empty(2, dtype=torch.int64, device=dev)
+    ws = torch.empty(max(int(_lib.gs_project_workspace_bytes(n)), 16), dtype=torch.uint8, device=dev)
+    _capi.check(_lib.gs_project_cull_sh(
+        xyz.data_ptr(), feat.data_ptr(), inv.data_ptr(), oid.data_ptr(), n, Kmat.data_ptr(),
+        st.q_cam.data_ptr(), st.t_cam.data_ptr(), n_obj, float(cfg.near_plane),
+        float(cfg.far_plane), W, H, float(cfg.depth_to_sort_key_scale),
+        buf.ptr("ids"), buf.ptr("point_uv"), buf.ptr("point_in_camera"), buf.ptr("conic"),
+        buf.ptr("alpha"), buf.ptr("color"), buf.ptr("radii"), buf.ptr("num_tiles"),
+        buf.ptr("tile_offsets"), buf.ptr("records"), buf.ptr("bbox"), buf.ptr("depth_key"),
+        totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
+    m, k = (int(v) for v in totals.tolist())  # the one host sync of the forward
+    st.m, st.k = m, k
+
+    num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
+    st.tile_start = torch.empty(num_tiles, dtype=torch.int32, device=dev)
+    st.tile_end = torch.empty(num_tiles, dtype=torch.int32, device=dev)
+    st.image = torch.empty(H, W, 3, dtype=torch.float32, device=dev)
+    rgb_only = bool(cfg.rgb_only)
+    if rgb_only:
+        # the reference leaves these uninitialised (R.py:478-484); zeros are the safe superset
+        st.depth = torch.zeros(H, W, dtype=torch.float32, device=dev)
+        st.acc_alpha = torch.zeros(H, W, dtype=torch.float32, device=dev)
+        st.last = torch.zeros(H, W, dtype=torch.int32, device=dev)
+        st.count = torch.zeros(H, W, dtype=torch.int32, device=dev)
+    else:
+        st.depth = torch.empty(H, W, dtype=torch.float32, device=dev)
+        st.acc_alpha = torch.empty(H, W, dtype=torch.float32, device=dev)
+        st.last = torch.empty(H, W, dtype=torch.int32, device=dev)
+        st.count = torch.empty(H, W, dtype=torch.int32, device=dev)
+
+    depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
+                                          float(cfg.depth_to_sort_key_scale), num_tiles)
+    keys2 = torch.empty(2 * max(k, 1), dtype=torch.int64, device=dev)
+    pay2 = torch.empty(2 * max(k, 1), dtype=torch.int32, device=dev)
+    keys_a, keys_b = keys2[:max(k, 1)], keys2[max(k, 1):]
+    pay_a, pay_b = pay2[:max(k, 1)], pay2[max(k, 1):]
+    if k > 0:
+        _capi.check(_lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"), buf.ptr("tile_offsets"),
+                                      m, k, W, keys_a.data_ptr(), pay_a.data_ptr(), stream),
+                    "gs_emit_keys")
+        if keep_unsorted:
+            st.unsorted_keys, st.unsorted_payload = keys_a[:k].clone(), pay_a[:k].clone()
+        sort_ws = torch.empty(int(_lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
+        in_alt = C.c_int(0)
+        _capi.check(_lib.gs_sort_pairs(keys_a.data_ptr(), pay_a.data_ptr(), keys_b.data_ptr(),
+                                       pay_b.data_ptr(), k, depth_bits, tile_bits,
+                                       sort_ws.data_ptr(), C.byref(in_alt), stream), "gs_sort_pairs")
+        st.keys = (keys_b if in_alt.value else keys_a)[:k]
+        st.payload = (pay_b if in_alt.value else pay_a)[:k]
+    else:
+        st.keys, st.payload = keys_a[:0], pay_a[:0]
+    _capi.check(_lib.gs_tile_ranges(st.keys.data_ptr() if k > 0 else None, k,
+                                    st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
+                                    stream), "gs_tile_ranges")
+    _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
+                                  st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
+                                  st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
+                                  st.last.data_ptr(), st.count.data_ptr(), int(rgb_only), stream),
+                "gs_blend_fwd")
+    st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
+                   tile_bits=tile_bits)
+    return st
+
+
+def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, point_object_id,
+                   t_pointcloud_camera, camera_info, color_max_sh_band, grad_rasterized_image,
+                   hook, hook_input_type):
+    dev = pointcloud.device
+    n, m, W, H = st.n, st.m, st.width, st.height
+    stream = torch.cuda.current_stream(dev).cuda_stream
+    grad_pointcloud = torch.zeros_like(pointcloud)
+    grad_features = torch.zeros_like(pointcloud_features, memory_format=torch.contiguous_format)
+    if grad_rasterized_image is None:
+        grad_rasterized_image = torch.zeros(H, W, 3, dtype=torch.float32, device=dev)
+    g_img = grad_rasterized_image.detach().to(torch.float32).contiguous()
+    on_image = torch.empty(H, W, 2, dtype=torch.float32, device=dev)
+    splat_grads = torch.zeros(max(m, 1), _GRAD_SLOTS, dtype=torch.float32, device=dev)
+    buf = st.buffers
+    _capi.check(_lib.gs_blend_bwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
+                                  st.payload.data_ptr() if st.k > 0 else None, buf.ptr("records"),
+                                  g_img.data_ptr(), st.acc_alpha.data_ptr(), st.last.data_ptr(),
+                                  splat_grads.data_ptr(), on_image.data_ptr(), stream),
+                "gs_blend_bwd")
+    want_hook = hook is not None
+    h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None
+    h_feat = torch.empty(m, 56, dtype=torch.float32, device=dev) if want_hook else None
+    h_view = torch.empty(m, 2, dtype=torch.float32, device=dev) if want_hook else None
+    h_mag = torch.empty(m, dtype=torch.float32, device=dev) if want_hook else None
+    h_aff = torch.empty(m, dtype=torch.int32, device=dev) if want_hook else None
+    t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
+    if m > 0:
+        _capi.check(_lib.gs_point_bwd(
+            pointcloud.detach().contiguous().data_ptr(), pointcloud_features.detach().data_ptr(),
+            point_object_id.contiguous().data_ptr(), st.intrinsics.data_ptr(), st.q_cam.data_ptr(),
+            st.t_cam.data_ptr(), t_pc.data_ptr(), st.q_cam.shape[0], buf.ptr("ids"), m,
+            buf.ptr("point_in_camera"), splat_grads.data_ptr(), int(color_max_sh_band),
+            float(cfg.grad_q_factor), float(cfg.grad_s_factor), float(cfg.grad_alpha_factor),
+            float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
+            grad_pointcloud.data_ptr(), grad_features.data_ptr(), _ptr(h_xyz), _ptr(h_feat),
+            _ptr(h_view), _ptr(h_mag), _ptr(h_aff), stream), "gs_point_bwd")
+    if want_hook:
+        point_in_camera = buf.view("point_in_camera", m)
+        hook(hook_input_type(
+            point_id_in_camera_list=buf.view("ids", m),
+            grad_point_in_camera=h_xyz,
+            grad_pointfeatures_in_camera=h_feat,
+            grad_viewspace=h_view,
+            magnitude_grad_viewspace=h_mag,
+            magnitude_grad_viewspace_on_image=on_image,
+            num_overlap_tiles=buf.view("num_tiles", m),
+            num_affected_pixels=h_aff,
+            point_depth=point_in_camera[:, 2],
+            point_uv_in_camera=buf.view("point_uv", m),
+        ))
+    st.info["magnitude_grad_viewspace_on_image"] = on_image
+    st.info["splat_grads"] = splat_grads
+    return grad_pointcloud, grad_features
+
+
+def install() -> None:
+    """Make the reference package use this operator (trainer, renderer and tests unchanged).
+
+    Replaces the class attribute in the already-importable reference module; raises ImportError
+    if the reference package (and its Taichi dependency) is not importable.
+    """
+    import importlib
+    ref = importlib.import_module("taichi_3d_gaussian_splatting.GaussianPointCloudRasterisation")
+    ref.GaussianPointCloudRasterisation = GaussianPointCloudRasterisation
+    ref.find_tile_start_and_end = find_tile_start_and_end
+    pkg = importlib.import_module("taichi_3d_gaussian_splatting")
+    if hasattr(pkg, "GaussianPointCloudRasterisation"):
+        setattr(pkg, "GaussianPointCloudRasterisation", ref)

@@ -1,0 +1,68 @@
+"""ctypes binding of libgs_b200.so, the C ABI declared in include/gs_b200.h.
+
+The library is built in-tree by `build.py` (nvcc, sm_100a).  There is no CPU or
+PyTorch fallback: if the library cannot be loaded (and cannot be built), importing
+this module raises, and so does every rasteriser call.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+from . import build as _build
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
+
+ABI_VERSION = 100
+
+_p = C.c_void_p
+_i = C.c_int
+_l = C.c_int64
+_f = C.c_float
+
+# name -> (restype, argtypes); must list every symbol of include/gs_b200.h
+SIGNATURES = {
+    "gs_abi_version": (_i, []),
+    "gs_status_string": (C.c_char_p, [_i]),
+    "gs_project_workspace_bytes": (_l, [_l]),
+    "gs_sort_workspace_bytes": (_l, [_l]),
+    "gs_inverse_pose": (_i, [_p, _p, _i, _p, _p, _p]),
+    "gs_project_cull_sh": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
+                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "gs_emit_keys": (_i, [_p, _p, _p, _l, _l, _i, _p, _p, _p]),
+    "gs_sort_pairs": (_i, [_p, _p, _p, _p, _l, _i, _i, _p, C.POINTER(C.c_int), _p]),
+    "gs_tile_ranges": (_i, [_p, _l, _p, _p, _i, _p]),
+    "gs_blend_fwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "gs_blend_bwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "gs_point_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p, _p, _i, _f, _f, _f, _f, _f,
+                          _p, _p, _p, _p, _p, _p, _p, _p]),
+}
+
+
+class GsError(RuntimeError):
+    pass
+
+
+def _load() -> C.CDLL:
+    if not os.path.exists(LIB_PATH) or os.environ.get("GS_B200_REBUILD") == "1":
+        # raises if nvcc is missing or the compile fails: no fallback path exists
+        _build.build(force=os.environ.get("GS_B200_REBUILD") == "1")
+    lib = C.CDLL(LIB_PATH)
+    for name, (restype, argtypes) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError here means header and library disagree
+        fn.restype = restype
+        fn.argtypes = argtypes
+    got = lib.gs_abi_version()
+    if got != ABI_VERSION:
+        raise GsError(f"libgs_b200.so ABI {got} != expected {ABI_VERSION}; rebuild with build.py")
+    return lib
+
+
+lib = _load()
+
+
+def check(status: int, what: str) -> None:
+    if status != 0:
+        msg = lib.gs_status_string(status)
+        raise GsError(f"{what} failed: status {status} ({msg.decode() if msg else '?'})")

@@ -1,0 +1,13 @@
+// capi.cu -- ABI identification and status strings of libgs_b200.so (see include/gs_b200.h).
+#include "gs_common.cuh"
+
+extern "C" int gs_abi_version(void) { return 100; }
+
+extern "C" const char *gs_status_string(int status)
+{
+    if (status == GS_OK) return "ok";
+    if (status == GS_E_INVALID) return "invalid argument";
+    if (status == GS_E_CAPACITY) return "count exceeds the int32 / 30-bit index contract";
+    if (status > 0) return cudaGetErrorString((cudaError_t)status);
+    return "unknown status";
+}

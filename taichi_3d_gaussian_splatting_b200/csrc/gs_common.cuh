@@ -1,0 +1,107 @@
+// Shared device helpers for the sm_100a rasteriser kernels.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "gs_b200.h"
+
+#define GS_LAUNCH_CHECK()                          \
+    do {                                           \
+        cudaError_t e__ = cudaGetLastError();      \
+        if (e__ != cudaSuccess) return (int)e__;   \
+    } while (0)
+
+#define GS_CUDA_TRY(expr)                          \
+    do {                                           \
+        cudaError_t e__ = (expr);                  \
+        if (e__ != cudaSuccess) return (int)e__;   \
+    } while (0)
+
+constexpr int kTile = GS_TILE;
+constexpr int kTilePixels = GS_TILE * GS_TILE;
+constexpr int kRecFloats = GS_RECORD_FLOATS;
+constexpr int kGradSlots = GS_GRAD_SLOTS;
+
+// exp of the literal-fp32 profile: Cody-Waite reduction + Cephes polynomial with fma at
+// fixed places.  Must stay operation-for-operation identical to gso_expf in
+// oracle/gs_oracle.c (the translation units that use it are built with -fmad=false, so
+// only the explicit fmaf calls fuse).
+__device__ __forceinline__ float gs_expf_core(float x)
+{
+    float t = x * 1.44269504088896341f;
+    float j = (t + 12582912.0f) - 12582912.0f;
+    float f = fmaf(j, -0.693145751953125f, x);
+    f = fmaf(j, -1.42860682030941723212e-6f, f);
+    float p = 1.9875691500e-4f;
+    p = fmaf(p, f, 1.3981999507e-3f);
+    p = fmaf(p, f, 8.3334519073e-3f);
+    p = fmaf(p, f, 4.1665795894e-2f);
+    p = fmaf(p, f, 1.6666665459e-1f);
+    p = fmaf(p, f, 5.0000001201e-1f);
+    float f2 = f * f;
+    float r = fmaf(p, f2, f) + 1.0f;
+    int ji = (int)j;
+    return __int_as_float(__float_as_int(r) + (ji << 23));
+}
+
+__device__ __forceinline__ float gs_expf(float x)
+{
+    if (!(x >= -87.0f)) return (x != x) ? x : 0.0f;
+    if (x > 88.0f) return __int_as_float(0x7f800000);
+    return gs_expf_core(x);
+}
+
+__device__ __forceinline__ float gs_sigmoid(float x) { return 1.0f / (1.0f + gs_expf(-x)); }
+
+// reference GaussianPoint3D.py:30-48
+__device__ __forceinline__ void gs_rotation_from_quaternion(float x, float y, float z, float w,
+                                                            float R[9])
+{
+    float xx = x * x, yy = y * y, zz = z * z;
+    float xy = x * y, xz = x * z, yz = y * z;
+    float wx = w * x, wy = w * y, wz = w * z;
+    R[0] = 1.0f - 2.0f * (yy + zz); R[1] = 2.0f * (xy - wz);        R[2] = 2.0f * (xz + wy);
+    R[3] = 2.0f * (xy + wz);        R[4] = 1.0f - 2.0f * (xx + zz); R[5] = 2.0f * (yz - wx);
+    R[6] = 2.0f * (xz - wy);        R[7] = 2.0f * (yz + wx);        R[8] = 1.0f - 2.0f * (xx + yy);
+}
+
+// reference SphericalHarmonics.py:10-32 (direction is normalised first)
+__device__ __forceinline__ void gs_sh_basis(float dx, float dy, float dz, float b[16])
+{
+    float s = (dx * dx + dy * dy) + dz * dz;
+    float inv = 1.0f / sqrtf(s);
+    float x = inv * dx, y = inv * dy, z = inv * dz;
+    b[0] = (float)0.28209479177387814;
+    b[1] = (float)-0.48860251190291987 * y;
+    b[2] = (float)0.48860251190291987 * z;
+    b[3] = (float)-0.48860251190291987 * x;
+    b[4] = (float)1.0925484305920792 * x * y;
+    b[5] = (float)-1.0925484305920792 * y * z;
+    b[6] = (float)0.94617469575755997 * z * z - (float)0.31539156525251999;
+    b[7] = (float)-1.0925484305920792 * x * z;
+    b[8] = (float)0.54627421529603959 * x * x - (float)0.54627421529603959 * y * y;
+    b[9] = (float)0.59004358992664352 * y * (-3.0f * x * x + y * y);
+    b[10] = (float)2.8906114426405538 * x * y * z;
+    b[11] = (float)0.45704579946446572 * y * (1.0f - 5.0f * z * z);
+    b[12] = (float)0.3731763325901154 * z * (5.0f * z * z - 3.0f);
+    b[13] = (float)0.45704579946446572 * x * (1.0f - 5.0f * z * z);
+    b[14] = (float)1.4453057213202769 * z * (x * x - y * y);
+    b[15] = (float)0.59004358992664352 * x * (-x * x + 3.0f * y * y);
+}
+
+__device__ __forceinline__ unsigned long long gs_ld_volatile_u64(const unsigned long long *p)
+{
+    return *reinterpret_cast<const volatile unsigned long long *>(p);
+}
+__device__ __forceinline__ void gs_st_volatile_u64(unsigned long long *p, unsigned long long v)
+{
+    *reinterpret_cast<volatile unsigned long long *>(p) = v;
+}
+__device__ __forceinline__ uint32_t gs_ld_volatile_u32(const uint32_t *p)
+{
+    return *reinterpret_cast<const volatile uint32_t *>(p);
+}
+__device__ __forceinline__ void gs_st_volatile_u32(uint32_t *p, uint32_t v)
+{
+    *reinterpret_cast<volatile uint32_t *>(p) = v;
+}

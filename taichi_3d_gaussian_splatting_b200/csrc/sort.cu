@@ -1,0 +1,273 @@
+// sort.cu -- stable LSD radix sort of (int64 key, int32 payload) pairs, onesweep style:
+// one histogram pass over the keys, then one read + one scattered write per 8-bit digit with
+// a decoupled look-back over the per-tile digit counts (no separate scan pass).
+//
+// Replaces Tensor.sort() + gather (reference R.py:947-950).  Ties keep their input order
+// (emission-slot order), which fixes the order torch leaves unspecified.
+//
+// Only the significant bits are sorted.  A key is depth + (tile << 32); the host passes how many
+// low bits the depth needs and how many bits the tile id needs, and the digits are taken from the
+// compacted value (tile << depth_bits) | depth.  depth_bits = tile_bits = 32 selects a full
+// signed 64-bit sort (sign bit flipped), used when depths may be negative.
+#include "gs_common.cuh"
+
+namespace {
+
+constexpr int kRadix = 256;
+constexpr int kSortBlock = 256;
+constexpr int kSortWarps = kSortBlock / 32;
+constexpr int kItems = 16;
+constexpr int kSortTile = kSortBlock * kItems;
+constexpr int kMaxPasses = 8;
+constexpr uint32_t kStatAggregate = 1u << 30;
+constexpr uint32_t kStatPrefix = 2u << 30;
+constexpr uint32_t kStatMask = (1u << 30) - 1;
+
+struct KeySpec {
+    int depth_bits;
+    unsigned long long depth_mask;
+    unsigned long long xor_mask;
+};
+
+__device__ __forceinline__ unsigned long long compact_key(long long key, const KeySpec &s)
+{
+    unsigned long long u = (unsigned long long)key;
+    unsigned long long hi = u >> 32, lo = u & 0xffffffffull;
+    unsigned long long c = (s.depth_bits >= 32) ? u : ((hi << s.depth_bits) | (lo & s.depth_mask));
+    return c ^ s.xor_mask;
+}
+
+__global__ void __launch_bounds__(256)
+histogram_kernel(const long long *__restrict__ keys, long long k, KeySpec spec, int num_passes,
+                 uint32_t *__restrict__ ghist)
+{
+    __shared__ uint32_t sh[kMaxPasses * kRadix];
+    for (int i = threadIdx.x; i < num_passes * kRadix; i += blockDim.x) sh[i] = 0;
+    __syncthreads();
+    long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < k; i += stride) {
+        unsigned long long c = compact_key(keys[i], spec);
+        for (int p = 0; p < num_passes; ++p)
+            atomicAdd(&sh[p * kRadix + (int)((c >> (8 * p)) & 0xff)], 1u);
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < num_passes * kRadix; i += blockDim.x)
+        if (sh[i]) atomicAdd(&ghist[i], sh[i]);
+}
+
+// exclusive scan of each pass's 256-bin histogram; one block of 256 threads per pass
+__global__ void __launch_bounds__(256)
+scan_histogram_kernel(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ gbase)
+{
+    __shared__ uint32_t s_warp[kSortWarps];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t v = ghist[blockIdx.x * kRadix + tid];
+    uint32_t incl = v;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    gbase[blockIdx.x * kRadix + tid] = off + incl - v;
+}
+
+__global__ void __launch_bounds__(kSortBlock)
+onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
+                long long *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
+                KeySpec spec, int shift, const uint32_t *__restrict__ gbase,
+                uint32_t *__restrict__ status, unsigned int *__restrict__ ticket)
+{
+    extern __shared__ __align__(16) unsigned char smem[];
+    long long *s_keys = reinterpret_cast<long long *>(smem);
+    int32_t *s_vals = reinterpret_cast<int32_t *>(s_keys + kSortTile);
+    uint32_t *s_warp_hist = reinterpret_cast<uint32_t *>(s_vals + kSortTile);
+    uint32_t *s_digit_base = s_warp_hist + kSortWarps * kRadix;
+    uint32_t *s_global_off = s_digit_base + kRadix;
+    uint32_t *s_scan = s_global_off + kRadix;  // kSortWarps entries
+    __shared__ unsigned int s_ticket;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) s_warp_hist[w * kRadix + tid] = 0;
+    __syncthreads();
+    const long long tile = s_ticket;
+    const long long tile_base = tile * kSortTile;
+    const int valid = (int)min((long long)kSortTile, k - tile_base);
+
+    long long key[kItems];
+    int32_t val[kItems];
+    const int warp_first = warp * (kItems * 32);
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        int local = warp_first + j * 32 + lane;
+        if (local < valid) {
+            key[j] = keys_in[tile_base + local];
+            val[j] = vals_in[tile_base + local];
+        } else {
+            key[j] = 0;
+            val[j] = 0;
+        }
+    }
+
+    // ---- warp-level stable ranking per digit (match.any) ---------------------------------
+    uint32_t rank[kItems];
+    const unsigned int lanemask_lt = (1u << lane) - 1u;
+    uint32_t *my_hist = s_warp_hist + warp * kRadix;
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        int local = warp_first + j * 32 + lane;
+        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : 255;
+        unsigned int peers = __match_any_sync(0xffffffffu, d);
+        int leader = __ffs(peers) - 1;
+        uint32_t old = 0;
+        if (lane == leader) {
+            old = my_hist[d];
+            my_hist[d] = old + (uint32_t)__popc(peers);
+        }
+        old = __shfl_sync(0xffffffffu, old, leader);
+        rank[j] = old + (uint32_t)__popc(peers & lanemask_lt);
+        __syncwarp();
+    }
+    __syncthreads();
+
+    // ---- per-digit exclusive scan over warps; thread `tid` owns digit `tid` -----------------
+    uint32_t block_count = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w) {
+        uint32_t c = s_warp_hist[w * kRadix + tid];
+        s_warp_hist[w * kRadix + tid] = block_count;
+        block_count += c;
+    }
+    // the padding items of the last tile sit in digit 255 and must not be published
+    uint32_t publish_count = block_count;
+    if (tid == 255) publish_count -= (uint32_t)(kSortTile - valid);
+    gs_st_volatile_u32(status + tile * kRadix + tid,
+                       (tile == 0 ? kStatPrefix : kStatAggregate) | publish_count);
+
+    // exclusive scan of block_count over the 256 digits
+    uint32_t incl = block_count;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        uint32_t o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_scan[warp] = incl;
+    __syncthreads();
+    uint32_t warp_off = 0;
+#pragma unroll
+    for (int w = 0; w < kSortWarps; ++w)
+        if (w < warp) warp_off += s_scan[w];
+    const uint32_t digit_base = warp_off + incl - block_count;
+    s_digit_base[tid] = digit_base;
+    __syncthreads();
+
+    // ---- scatter the tile into shared memory in digit order -----------------------------------
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        int local = warp_first + j * 32 + lane;
+        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : 255;
+        uint32_t pos = s_digit_base[d] + my_hist[d] + rank[j];
+        s_keys[pos] = key[j];
+        s_vals[pos] = val[j];
+    }
+
+    // ---- decoupled look-back for digit `tid` -----------------------------------------------
+    uint32_t excl = 0;
+    if (tile > 0) {
+        long long b = tile - 1;
+        while (true) {
+            uint32_t s;
+            do { s = gs_ld_volatile_u32(status + b * kRadix + tid); } while ((s >> 30) == 0);
+            excl += s & kStatMask;
+            if ((s >> 30) == 2) break;
+            --b;
+        }
+        gs_st_volatile_u32(status + tile * kRadix + tid, kStatPrefix | (excl + publish_count));
+    }
+    s_global_off[tid] = gbase[tid] + excl - digit_base;  // unsigned wrap-around is intended
+    __syncthreads();
+
+    // ---- coalesced write-out: consecutive smem slots of one digit are consecutive in global -----
+    for (int i = tid; i < valid; i += kSortBlock) {
+        long long kk = s_keys[i];
+        int d = (int)((compact_key(kk, spec) >> shift) & 0xff);
+        uint32_t pos = (uint32_t)i + s_global_off[d];
+        keys_out[pos] = kk;
+        vals_out[pos] = s_vals[i];
+    }
+}
+
+constexpr size_t kSortSmem = (size_t)kSortTile * 12 + (size_t)kSortWarps * kRadix * 4 +
+                             (size_t)kRadix * 8 + (size_t)kSortWarps * 4;
+
+inline int64_t sort_tiles(int64_t k) { return (k + kSortTile - 1) / kSortTile; }
+
+}  // namespace
+
+extern "C" int64_t gs_sort_workspace_bytes(int64_t k)
+{
+    // ghist | gbase | tickets (64 B) | status[passes][tiles][256]
+    return (int64_t)kMaxPasses * kRadix * 4 * 2 + 64 + (int64_t)kMaxPasses * sort_tiles(k) * kRadix * 4;
+}
+
+extern "C" int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt,
+                             int32_t *payload_alt, int64_t k, int depth_bits, int tile_bits,
+                             void *workspace, int *result_in_alt, void *stream)
+{
+    if (result_in_alt) *result_in_alt = 0;
+    if (k < 0 || depth_bits < 0 || depth_bits > 32 || tile_bits < 0 || tile_bits > 32)
+        return GS_E_INVALID;
+    if (k >= (1ll << 30)) return GS_E_CAPACITY;  // 30-bit counts in the look-back words
+    if (k <= 1) return GS_OK;
+    if (!keys || !payload || !keys_alt || !payload_alt || !workspace) return GS_E_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    KeySpec spec;
+    spec.depth_bits = depth_bits;
+    spec.depth_mask = depth_bits >= 32 ? 0xffffffffull : ((1ull << depth_bits) - 1ull);
+    const bool full = (depth_bits == 32 && tile_bits == 32);
+    spec.xor_mask = full ? 0x8000000000000000ull : 0ull;
+    int total_bits = depth_bits + tile_bits;
+    int num_passes = (total_bits + 7) / 8;
+    if (num_passes == 0) return GS_OK;
+
+    const int64_t tiles = sort_tiles(k);
+    uint32_t *ghist = (uint32_t *)workspace;
+    uint32_t *gbase = ghist + kMaxPasses * kRadix;
+    unsigned int *tickets = (unsigned int *)(gbase + kMaxPasses * kRadix);
+    uint32_t *status = (uint32_t *)(tickets + 16);
+    size_t used = (size_t)kMaxPasses * kRadix * 4 * 2 + 64 + (size_t)num_passes * tiles * kRadix * 4;
+    GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, used, st));
+
+    static bool attr_set = false;
+    if (!attr_set) {
+        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)kSortSmem));
+        attr_set = true;
+    }
+
+    int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
+    if (hist_blocks < 1) hist_blocks = 1;
+    histogram_kernel<<<hist_blocks, 256, 0, st>>>((const long long *)keys, k, spec, num_passes, ghist);
+    GS_LAUNCH_CHECK();
+    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ghist, gbase);
+    GS_LAUNCH_CHECK();
+
+    long long *kin = (long long *)keys, *kout = (long long *)keys_alt;
+    int32_t *vin = payload, *vout = payload_alt;
+    for (int p = 0; p < num_passes; ++p) {
+        onesweep_kernel<<<(unsigned)tiles, kSortBlock, kSortSmem, st>>>(
+            kin, vin, kout, vout, k, spec, 8 * p, gbase + p * kRadix,
+            status + (size_t)p * tiles * kRadix, tickets + p);
+        GS_LAUNCH_CHECK();
+        long long *tk = kin; kin = kout; kout = tk;
+        int32_t *tv = vin; vin = vout; vout = tv;
+    }
+    if (result_in_alt) *result_in_alt = (num_passes & 1);
+    return GS_OK;
+}

@@ -1,0 +1,298 @@
+"""GPU tests of single C-ABI entry points (sort, ranges, key emission) and of the operator's
+edge cases (empty frustum, empty key list, rgb_only, hook-less backward, full-size run)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
+
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+def _lib():
+    from taichi_3d_gaussian_splatting_b200 import _capi
+    return _capi
+
+
+def _sort_pairs(keys_np, depth_bits, tile_bits):
+    capi = _lib()
+    k = keys_np.shape[0]
+    dev = torch.device("cuda")
+    keys = torch.from_numpy(keys_np.copy()).to(dev)
+    vals = torch.arange(k, dtype=torch.int32, device=dev)
+    keys_alt, vals_alt = torch.empty_like(keys), torch.empty_like(vals)
+    ws = torch.empty(int(capi.lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
+    in_alt = C.c_int(0)
+    st = torch.cuda.current_stream().cuda_stream
+    capi.check(capi.lib.gs_sort_pairs(keys.data_ptr(), vals.data_ptr(), keys_alt.data_ptr(),
+                                      vals_alt.data_ptr(), k, depth_bits, tile_bits, ws.data_ptr(),
+                                      C.byref(in_alt), st), "gs_sort_pairs")
+    torch.cuda.synchronize()
+    rk, rv = (keys_alt, vals_alt) if in_alt.value else (keys, vals)
+    return rk.cpu().numpy(), rv.cpu().numpy()
+
+
+@pytest.mark.parametrize("k", [1, 2, 31, 4095, 4096, 4097, 12289, 300001, 3000000])
+@pytest.mark.parametrize("bits", [(17, 13), (15, 12), (8, 1), (5, 3)])
+def test_sort_significant_bits_stable(k, bits):
+    depth_bits, tile_bits = bits
+    rng = np.random.default_rng(k * 31 + depth_bits)
+    # few distinct depths -> many ties, so stability is really exercised
+    depth = rng.integers(0, min(1 << depth_bits, 50), k, dtype=np.int64)
+    tile = rng.integers(0, 1 << tile_bits, k, dtype=np.int64)
+    keys = depth + (tile << 32)
+    sk, sv = _sort_pairs(keys, depth_bits, tile_bits)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(sk, keys[order])
+    assert np.array_equal(sv, order.astype(np.int32))
+
+
+@pytest.mark.parametrize("k", [5, 4097, 100000])
+def test_sort_full_signed_64bit(k):
+    rng = np.random.default_rng(k)
+    keys = rng.integers(-2**40, 2**40, k, dtype=np.int64)
+    keys[::7] = keys[0]
+    sk, sv = _sort_pairs(keys, 32, 32)
+    order = np.argsort(keys, kind="stable")
+    assert np.array_equal(sk, keys[order])
+    assert np.array_equal(sv, order.astype(np.int32))
+
+
+def test_tile_ranges_reference_golden_vector():
+    """tests/GaussianPointCloudRasterisation_test.py:18-51 of the reference, same call."""
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import find_tile_start_and_end
+    keys = torch.tensor([0x100000000, 0x100000001, 0x200000000, 0x200000001, 0x200000002,
+                         0x300000000, 0x300000001], dtype=torch.int64, device="cuda")
+    start = torch.zeros(4, dtype=torch.int32, device="cuda")
+    end = torch.zeros(4, dtype=torch.int32, device="cuda")
+    find_tile_start_and_end(keys, start, end)
+    assert start.tolist() == [0, 0, 2, 5]
+    assert end.tolist() == [0, 2, 5, 7]
+
+
+def test_emit_keys_large_and_empty_boxes(oracle32):
+    """Splats covering the whole image, single-tile splats and zero-tile splats mixed."""
+    capi = _lib()
+    W, H = 320, 208
+    tw, th = W // 16, H // 16
+    rng = np.random.default_rng(5)
+    m = 1500
+    uv = np.stack([rng.uniform(-40, W + 40, m), rng.uniform(-40, H + 40, m)], 1).astype(np.float32)
+    radii = np.exp(rng.uniform(np.log(0.5), np.log(400.0), m)).astype(np.float32)
+    radii[::11] = 5000.0
+    pic = np.zeros((m, 3), np.float32)
+    pic[:, 2] = rng.uniform(1, 900, m)
+    counts = oracle32.tile_counts(uv, radii, W, H)
+    assert (counts == 0).any() and (counts == tw * th).any()
+    offsets, total = oracle32.exclusive_scan(counts)
+    keys_ref, pay_ref = oracle32.emit_keys(uv, pic, radii, offsets, total, W, H, 100.0)
+    # bbox / depth key exactly as the projection kernel would hand them over
+    bbox = np.zeros((m, 4), np.uint16)
+    for i in range(m):
+        r = max(radii[i], np.float32(1.0))
+        mn_u, mx_u = max(np.float32(0), uv[i, 0] - r), uv[i, 0] + r
+        mn_v, mx_v = max(np.float32(0), uv[i, 1] - r), uv[i, 1] + r
+        tu0 = min(int(np.floor(mn_u / 16)), tw)
+        tu1 = min(max(int(np.floor(mx_u / 16)) + 1, tu0 + 1), tw)
+        tv0 = min(int(np.floor(mn_v / 16)), th)
+        tv1 = min(max(int(np.floor(mx_v / 16)) + 1, tv0 + 1), th)
+        bbox[i] = (tu0, tu1, tv0, tv1)
+    assert np.array_equal((bbox[:, 1].astype(int) - bbox[:, 0]) * (bbox[:, 3].astype(int) - bbox[:, 2]),
+                          counts)
+    depth_key = (pic[:, 2] * np.float32(100.0)).astype(np.int32)
+    dev = torch.device("cuda")
+    d_bbox = torch.from_numpy(bbox.view(np.int16)).to(dev)
+    d_depth = torch.from_numpy(depth_key).to(dev)
+    d_off = torch.from_numpy(offsets).to(dev)
+    keys = torch.empty(total, dtype=torch.int64, device=dev)
+    pay = torch.empty(total, dtype=torch.int32, device=dev)
+    capi.check(capi.lib.gs_emit_keys(d_bbox.data_ptr(), d_depth.data_ptr(), d_off.data_ptr(), m,
+                                     total, W, keys.data_ptr(), pay.data_ptr(),
+                                     torch.cuda.current_stream().cuda_stream), "gs_emit_keys")
+    torch.cuda.synchronize()
+    assert np.array_equal(keys.cpu().numpy(), keys_ref)
+    assert np.array_equal(pay.cpu().numpy(), pay_ref)
+
+
+def _module(near=0.8, far=1000.0, scale=100.0, rgb_only=False, hook=None):
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
+    return GaussianPointCloudRasterisation(
+        GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig(
+            near_plane=near, far_plane=far, depth_to_sort_key_scale=scale, rgb_only=rgb_only),
+        backward_valid_point_hook=hook)
+
+
+def _call(ras, scene, t, band=2):
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
+    cam = CameraInfo(t["camera_intrinsics"], scene.height, scene.width, 0)
+    return ras(GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput(
+        point_cloud=t["point_cloud"], point_cloud_features=t["point_cloud_features"],
+        point_object_id=t["point_object_id"], point_invalid_mask=t["point_invalid_mask"],
+        camera_info=cam, q_pointcloud_camera=t["q_pointcloud_camera"],
+        t_pointcloud_camera=t["t_pointcloud_camera"], color_max_sh_band=band))
+
+
+def test_empty_frustum_gives_zero_image_and_zero_grads():
+    scene = make_scene(500, 64, 48, seed=9, scale_factor=0.05)
+    scene.point_invalid_mask[:] = 1
+    t = util.scene_tensors(scene, requires_grad=True)
+    hooked = {}
+    ras = _module(hook=lambda h: hooked.update(h=h))
+    image, depth, count = _call(ras, scene, t)
+    assert image.shape == (48, 64, 3) and depth.shape == (48, 64) and count.dtype == torch.int32
+    assert float(image.abs().max()) == 0 and int(count.max()) == 0
+    image.sum().backward()
+    assert float(t["point_cloud"].grad.abs().max()) == 0
+    assert float(t["point_cloud_features"].grad.abs().max()) == 0
+    assert hooked["h"].point_id_in_camera_list.shape[0] == 0
+    assert ras.last_forward_info["num_points_in_camera"] == 0
+
+
+def test_visible_points_with_zero_tiles(oracle32):
+    """Points inside the 48 px margin right of / below the image are visible but touch no tile
+    (R.py:94-102): M > 0, K == 0."""
+    scene = make_scene(200, 64, 64, seed=10, scale_factor=0.001)
+    f = 0.6 * 64
+    z = scene.point_cloud[:, 2]
+    scene.point_cloud[:, 0] = (64 + 20 - 32) * z / f   # u = W + 20
+    scene.point_invalid_mask[:] = 0
+    ref = util.oracle_forward(oracle32, scene)
+    assert len(ref["point_id_in_camera_list"]) == 200 and len(ref["point_in_camera_sort_key"]) == 0
+    got = util.cuda_forward_stages(scene)
+    assert not util.mismatch_report(ref, got)
+
+
+def test_rgb_only_matches_image(oracle32):
+    scene = make_scene(2000, 64, 64, seed=11, scale_factor=0.05)
+    ref = util.oracle_forward(oracle32, scene, rgb_only=True)
+    got = util.cuda_forward_stages(scene, rgb_only=True)
+    assert np.array_equal(ref["rasterized_image"], got["rasterized_image"])
+    assert not got["rasterized_depth"].any() and not got["pixel_valid_point_count"].any()
+
+
+def test_reference_two_points_case(oracle32):
+    """tests/GaussianPointCloudRasterisation_test.py:152-205 of the reference: two points on the
+    optical axis, the nearer one invalid, 16x16 image, near 0, far 10."""
+    from taichi_3d_gaussian_splatting_b200.synthetic import SyntheticScene
+    feat = np.zeros((2, 56), np.float32)
+    feat[:, 3] = 1.0
+    feat[0, 4:7] = 1.0
+    feat[1, 4:7] = 4.0
+    feat[:, 8] = 5.0
+    feat[:, 24] = 1.0
+    feat[:, 40] = 1.0
+    scene = SyntheticScene(np.array([[0, 0, 1], [0, 0, 2]], np.float32), feat,
+                           np.array([1, 0], np.int8), np.zeros(2, np.int32),
+                           np.array([[1, 0, 8], [0, 1, 8], [0, 0, 1]], np.float32),
+                           np.array([[0, 0, 0, 1]], np.float32), np.zeros((1, 3), np.float32), 16, 16)
+    ref = util.oracle_forward(oracle32, scene, 0.0, 10.0, 100.0)
+    got = util.cuda_forward_stages(scene, 0.0, 10.0, 100.0)
+    assert list(ref["point_id_in_camera_list"]) == [1]
+    assert not util.mismatch_report(ref, got)
+    assert got["rasterized_image"].max() > 0.1
+
+
+def test_inference_under_no_grad_and_input_validation():
+    scene = make_scene(3000, 64, 64, seed=12, scale_factor=0.05)
+    t = util.scene_tensors(scene)
+    ras = _module()
+    with torch.no_grad():
+        image, depth, count = _call(ras, scene, t)
+    assert image.requires_grad is False and torch.isfinite(image).all()
+    bad = dict(t)
+    bad["point_cloud_features"] = t["point_cloud_features"].double()
+    with pytest.raises(ValueError):
+        _call(ras, scene, bad)
+    scene_bad = make_scene(10, 64, 64, seed=1)
+    scene_bad.width = 60
+    with pytest.raises(AssertionError):  # R.py:1193-1194
+        _call(ras, scene_bad, util.scene_tensors(scene_bad))
+    cpu = util.scene_tensors(scene, device="cpu")
+    with pytest.raises(Exception):
+        _call(ras, scene, cpu)
+
+
+def test_training_loop_reduces_loss():
+    """Behavioural pin of reference test_backward_coverage (T_R.py:284-351), shortened: Adam on a
+    32x32 synthetic target, loss must go down."""
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
+    torch.manual_seed(0)
+    dev = "cuda"
+    n = 10000
+    target = torch.zeros(32, 32, 3, device=dev)
+    target[:5, :2, 0] = 1.0
+    target[:5, :2, 1] = 0.7
+    target[8:24, 8:24, 0] = 0.5
+    target[8:24, 8:24, 1] = 0.7
+    target[20:28, 20:28, 0] = 0.8
+    target[20:28, 20:28, 1] = 0.1
+    xyz = torch.nn.Parameter((torch.rand(n, 3, device=dev) - 0.5) * 3)
+    tmp = torch.rand(n, 56, device=dev)
+    tmp[:, 4:7] = -4.60517018599
+    tmp[:, 7] = 0.5
+    feat = torch.nn.Parameter(tmp)
+    cam = CameraInfo(torch.tensor([[32., 0, 16], [0, 32., 16], [0, 0, 1]], device=dev), 32, 32, 0)
+    q = torch.tensor([[0., 0, 0, 1]], device=dev)
+    tt = torch.tensor([[0., 0, 2.0]], device=dev)  # T_pointcloud_camera: camera 2 units behind
+    ras = GaussianPointCloudRasterisation(
+        GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig(near_plane=1., far_plane=10.))
+    opt = torch.optim.Adam([xyz, feat], lr=0.001)
+    inv = torch.zeros(n, dtype=torch.int8, device=dev)
+    oid = torch.zeros(n, dtype=torch.int32, device=dev)
+    losses = []
+    for it in range(300):
+        opt.zero_grad()
+        image, _, _ = ras(GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput(
+            point_cloud=xyz, point_cloud_features=feat, point_object_id=oid, point_invalid_mask=inv,
+            camera_info=cam, q_pointcloud_camera=q, t_pointcloud_camera=-tt,
+            color_max_sh_band=it // 100))
+        loss = ((image - target) ** 2).sum()
+        loss.backward()
+        opt.step()
+        losses.append(float(loss))
+    assert np.isfinite(losses).all()
+    assert losses[-1] < 0.7 * losses[0], (losses[0], losses[-1])
+
+
+def test_full_size_c2_against_oracle(oracle32, oracle64):
+    """BASELINE.json config 2 at full size: 1M Gaussians, 1920x1088, SH degree 3 -- every forward
+    stage value-exact against the oracle, gradients at 1e-4, plus size-independent properties."""
+    scene = make_scene(1_000_000, 1920, 1088, seed=1002, scale_factor=0.004)
+    got = util.cuda_forward_stages(scene)
+    keys = got["point_in_camera_sort_key"]
+    assert np.all(keys[1:] >= keys[:-1])
+    assert int(got["num_overlap_tiles"].sum()) == keys.shape[0]
+    pay = got["point_offset_with_sort_key"]
+    assert pay.min() >= 0 and pay.max() < got["point_id_in_camera_list"].shape[0]
+    assert np.array_equal(np.bincount(pay, minlength=got["num_overlap_tiles"].shape[0]),
+                          got["num_overlap_tiles"])
+    assert np.isfinite(got["rasterized_image"]).all()
+    lists = (got["tile_points_end"] - got["tile_points_start"]).reshape(1088 // 16, 1920 // 16)
+    per_pixel_len = np.repeat(np.repeat(lists, 16, 0), 16, 1)
+    assert np.all(got["pixel_valid_point_count"] <= per_pixel_len)
+    ref = util.oracle_forward(oracle32, scene)
+    report = util.mismatch_report(ref, got)
+    assert not report, "\n".join(report)
+
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
+    g = np.random.default_rng(3).uniform(0, 1, (1088, 1920, 3)).astype(np.float32)
+    ref64 = {k: (v.astype(np.float64) if isinstance(v, np.ndarray) and v.dtype == np.float32 else v)
+             for k, v in ref.items()}
+    b64 = oracle64.backward(ref64, g.astype(np.float64), 3)
+    t = util.scene_tensors(scene, requires_grad=True)
+    ras = _module()
+    image, _, _ = _call(ras, scene, t, band=3)
+    (image * torch.from_numpy(g).cuda()).sum().backward()
+    for name, cuda, o64 in (("xyz", t["point_cloud"].grad.cpu().numpy(), b64["grad_pointcloud"]),
+                            ("features", t["point_cloud_features"].grad.cpu().numpy(),
+                             b64["grad_pointcloud_features"])):
+        l2, mx = util.grad_error(o64, cuda)
+        print(f"C2 grad {name}: rel-l2 {l2:.2e} max-col-norm {mx:.2e}")
+        assert l2 <= 1e-4 and mx <= 1e-4

@@ -1,0 +1,132 @@
+"""Helpers shared by the parity tests: run the CUDA path stage by stage and name every buffer
+like the oracle (oracle/gs_oracle.py) does, so the two dicts can be diffed key by key."""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+
+def scene_tensors(scene, device="cuda", requires_grad=False):
+    t = dict(
+        point_cloud=torch.from_numpy(scene.point_cloud).to(device),
+        point_cloud_features=torch.from_numpy(scene.point_cloud_features.copy()).to(device),
+        point_invalid_mask=torch.from_numpy(scene.point_invalid_mask).to(device),
+        point_object_id=torch.from_numpy(scene.point_object_id).to(device),
+        camera_intrinsics=torch.from_numpy(scene.camera_intrinsics).to(device),
+        q_pointcloud_camera=torch.from_numpy(scene.q_pointcloud_camera).to(device),
+        t_pointcloud_camera=torch.from_numpy(scene.t_pointcloud_camera).to(device),
+    )
+    if requires_grad:
+        t["point_cloud"].requires_grad_(True)
+        t["point_cloud_features"].requires_grad_(True)
+    return t
+
+
+def oracle_forward(oracle, scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False):
+    return oracle.forward(scene.point_cloud, scene.point_cloud_features, scene.point_invalid_mask,
+                          scene.point_object_id, scene.camera_intrinsics,
+                          scene.q_pointcloud_camera, scene.t_pointcloud_camera, scene.width,
+                          scene.height, near, far, scale, rgb_only)
+
+
+def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False):
+    """Run the product forward through its C ABI and return every stage as numpy arrays."""
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
+
+    t = scene_tensors(scene)
+    cfg = GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig(
+        near_plane=near, far_plane=far, depth_to_sort_key_scale=scale, rgb_only=rgb_only)
+    cam = CameraInfo(camera_intrinsics=t["camera_intrinsics"], camera_height=scene.height,
+                     camera_width=scene.width, camera_id=0)
+    st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"],
+                            t["point_invalid_mask"], t["point_object_id"],
+                            t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
+                            keep_unsorted=True)
+    torch.cuda.synchronize()
+    m, k, buf = st.m, st.k, st.buffers
+    np_ = lambda x: x.detach().cpu().numpy()
+    out = dict(
+        point_id_in_camera_list=np_(buf.view("ids", m)),
+        point_uv=np_(buf.view("point_uv", m)),
+        point_in_camera=np_(buf.view("point_in_camera", m)),
+        point_uv_conic_and_rescale=np_(buf.view("conic", m)),
+        point_alpha_after_activation=np_(buf.view("alpha", m)),
+        point_color=np_(buf.view("color", m)),
+        point_radii=np_(buf.view("radii", m)),
+        num_overlap_tiles=np_(buf.view("num_tiles", m)),
+        accumulated_num_overlap_tiles=np_(buf.view("tile_offsets", m)),
+        records=np_(buf.view("records", m)),
+        point_in_camera_sort_key=np_(st.keys),
+        point_offset_with_sort_key=np_(st.payload),
+        tile_points_start=np_(st.tile_start),
+        tile_points_end=np_(st.tile_end),
+        rasterized_image=np_(st.image),
+        rasterized_depth=np_(st.depth),
+        pixel_accumulated_alpha=np_(st.acc_alpha),
+        pixel_offset_of_last_effective_point=np_(st.last),
+        pixel_valid_point_count=np_(st.count),
+        q_camera_pointcloud=np_(st.q_cam),
+        t_camera_pointcloud=np_(st.t_cam),
+        features_out=np_(t["point_cloud_features"]),
+    )
+    if st.unsorted_keys is not None:
+        out["unsorted_keys"] = np_(st.unsorted_keys)
+        out["unsorted_payload"] = np_(st.unsorted_payload)
+    else:
+        out["unsorted_keys"] = np.zeros(0, np.int64)
+        out["unsorted_payload"] = np.zeros(0, np.int32)
+    out["_state"] = st
+    out["_tensors"] = t
+    return out
+
+
+FORWARD_KEYS_EXACT = [
+    "q_camera_pointcloud", "t_camera_pointcloud", "point_id_in_camera_list", "features_out",
+    "point_uv", "point_in_camera", "point_uv_conic_and_rescale", "point_alpha_after_activation",
+    "point_color", "point_radii", "num_overlap_tiles", "accumulated_num_overlap_tiles",
+    "unsorted_keys", "unsorted_payload", "point_in_camera_sort_key", "point_offset_with_sort_key",
+    "tile_points_start", "tile_points_end", "rasterized_image", "rasterized_depth",
+    "pixel_accumulated_alpha", "pixel_offset_of_last_effective_point", "pixel_valid_point_count",
+]
+
+
+def mismatch_report(ref: dict, got: dict, keys=FORWARD_KEYS_EXACT) -> list:
+    """Value-exact comparison (NaN == NaN, -0 == +0); returns one line per differing buffer."""
+    lines = []
+    for key in keys:
+        a, b = np.asarray(ref[key]), np.asarray(got[key])
+        if a.shape != b.shape:
+            lines.append(f"{key}: shape {a.shape} vs {b.shape}")
+            continue
+        if a.size == 0:
+            continue
+        if np.issubdtype(a.dtype, np.floating):
+            bad = ~((a == b) | (np.isnan(a) & np.isnan(b)))
+        else:
+            bad = a != b
+        nb = int(bad.sum())
+        if nb:
+            idx = np.argwhere(bad)[0]
+            if np.issubdtype(a.dtype, np.floating):
+                err = float(np.nanmax(np.abs(a.astype(np.float64) - b.astype(np.float64))[bad]))
+            else:
+                err = float(np.abs(a.astype(np.int64) - b.astype(np.int64))[bad].max())
+            lines.append(f"{key}: {nb}/{a.size} differ, first at {tuple(idx)}: "
+                         f"oracle {a[tuple(idx)]!r} cuda {b[tuple(idx)]!r}, max abs {err:.3e}")
+    return lines
+
+
+def grad_error(ref: np.ndarray, got: np.ndarray):
+    """(relative L2 error, max elementwise error normalised by the column's max magnitude)."""
+    ref = np.asarray(ref, np.float64)
+    got = np.asarray(got, np.float64)
+    denom = np.linalg.norm(ref)
+    rel_l2 = float(np.linalg.norm(ref - got) / denom) if denom > 0 else float(np.abs(got).max())
+    r2 = ref.reshape(ref.shape[0], -1)
+    g2 = got.reshape(got.shape[0], -1)
+    col = np.abs(r2).max(axis=0)
+    col[col == 0] = 1.0
+    max_norm = float((np.abs(r2 - g2) / col).max()) if r2.size else 0.0
+    return rel_l2, max_norm
