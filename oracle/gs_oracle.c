@@ -109,6 +109,12 @@ void gso_expf_array(const float *x, float *y, int64_t n)
     for (int64_t i = 0; i < n; ++i) y[i] = gso_expf(x[i]);
 }
 
+/* Optional tile-row band for the two blend loops: lets bench.py time a bounded sample of a
+ * large frame.  begin < 0 (default) = whole image.  Pixels outside the band are not written. */
+static int g_band_begin = -1, g_band_end = -1;
+void FN(set_tile_row_band)(int begin, int end) { g_band_begin = begin; g_band_end = end; }
+static int tile_in_band(int tile_v) { return g_band_begin < 0 || (tile_v >= g_band_begin && tile_v < g_band_end); }
+
 int FN(num_threads)(void)
 {
 #ifdef _OPENMP
@@ -512,6 +518,7 @@ void FN(blend_fwd)(int height, int width, const int32_t *tile_start, const int32
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : visited)
     for (int tile = 0; tile < tw * th; ++tile) {
         int tile_u = tile % tw, tile_v = tile / tw;
+        if (!tile_in_band(tile_v)) continue;
         int s = tile_start[tile], e = tile_end[tile];
         for (int o = 0; o < TILE * TILE; ++o) {
             int pu = tile_u * TILE + o % TILE, pv = tile_v * TILE + o / TILE;
@@ -568,6 +575,7 @@ void FN(blend_bwd)(int height, int width, const int32_t *tile_start, const int32
 #pragma omp parallel for schedule(dynamic, 1) reduction(+ : visited)
     for (int tile = 0; tile < tw * th; ++tile) {
         int tile_u = tile % tw, tile_v = tile / tw;
+        if (!tile_in_band(tile_v)) continue;
         int s = tile_start[tile], e = tile_end[tile];
         for (int o = 0; o < TILE * TILE; ++o) {
             int pu = tile_u * TILE + o % TILE, pv = tile_v * TILE + o / TILE;

@@ -64,6 +64,10 @@ class OracleLib:
     def num_threads(self) -> int:
         return int(self.fn("num_threads", C.c_int)())
 
+    def set_tile_row_band(self, begin: int = -1, end: int = -1) -> None:
+        """Restrict both blend loops to tile rows [begin, end) (bench.py's bounded CPU sample)."""
+        self.fn("set_tile_row_band")(C.c_int(begin), C.c_int(end))
+
     def inverse_pose(self, q_pc_cam, t_pc_cam):
         q = self.arr(q_pc_cam).reshape(-1, 4)
         t = self.arr(t_pc_cam).reshape(-1, 3)

@@ -38,6 +38,14 @@ _lib = _capi.lib
 _REC = 12
 _GRAD_SLOTS = 12
 
+# set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
+STAGE_PROFILER = None
+
+
+def _mark(name: str) -> None:
+    if STAGE_PROFILER is not None:
+        STAGE_PROFILER.mark(name)
+
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
@@ -276,6 +284,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     st = _ForwardState()
     st.n, st.width, st.height, st.intrinsics = n, W, H, Kmat
     st.unsorted_keys = st.unsorted_payload = None
+    _mark("forward_begin")
     st.q_cam = torch.empty_like(q_pc)
     st.t_cam = torch.empty_like(t_pc)
     _capi.check(_lib.gs_inverse_pose(q_pc.data_ptr(), t_pc.data_ptr(), n_obj, st.q_cam.data_ptr(),
@@ -293,6 +302,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         buf.ptr("alpha"), buf.ptr("color"), buf.ptr("radii"), buf.ptr("num_tiles"),
         buf.ptr("tile_offsets"), buf.ptr("records"), buf.ptr("bbox"), buf.ptr("depth_key"),
         totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
+    _mark("project_cull_sh")
     m, k = (int(v) for v in totals.tolist())  # the one host sync of the forward
     st.m, st.k = m, k
 
@@ -319,10 +329,12 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     pay2 = torch.empty(2 * max(k, 1), dtype=torch.int32, device=dev)
     keys_a, keys_b = keys2[:max(k, 1)], keys2[max(k, 1):]
     pay_a, pay_b = pay2[:max(k, 1)], pay2[max(k, 1):]
+    _mark("host_sync_and_alloc")
     if k > 0:
         _capi.check(_lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"), buf.ptr("tile_offsets"),
                                       m, k, W, keys_a.data_ptr(), pay_a.data_ptr(), stream),
                     "gs_emit_keys")
+        _mark("emit_keys")
         if keep_unsorted:
             st.unsorted_keys, st.unsorted_payload = keys_a[:k].clone(), pay_a[:k].clone()
         sort_ws = torch.empty(int(_lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
@@ -330,6 +342,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         _capi.check(_lib.gs_sort_pairs(keys_a.data_ptr(), pay_a.data_ptr(), keys_b.data_ptr(),
                                        pay_b.data_ptr(), k, depth_bits, tile_bits,
                                        sort_ws.data_ptr(), C.byref(in_alt), stream), "gs_sort_pairs")
+        _mark("sort_pairs")
         st.keys = (keys_b if in_alt.value else keys_a)[:k]
         st.payload = (pay_b if in_alt.value else pay_a)[:k]
     else:
@@ -337,11 +350,13 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     _capi.check(_lib.gs_tile_ranges(st.keys.data_ptr() if k > 0 else None, k,
                                     st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
                                     stream), "gs_tile_ranges")
+    _mark("tile_ranges")
     _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
                                   st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
                                   st.last.data_ptr(), st.count.data_ptr(), int(rgb_only), stream),
                 "gs_blend_fwd")
+    _mark("blend_fwd")
     st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
                    tile_bits=tile_bits)
     return st
@@ -353,6 +368,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
     stream = torch.cuda.current_stream(dev).cuda_stream
+    _mark("backward_begin")
     grad_pointcloud = torch.zeros_like(pointcloud)
     grad_features = torch.zeros_like(pointcloud_features, memory_format=torch.contiguous_format)
     if grad_rasterized_image is None:
@@ -361,11 +377,13 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     on_image = torch.empty(H, W, 2, dtype=torch.float32, device=dev)
     splat_grads = torch.zeros(max(m, 1), _GRAD_SLOTS, dtype=torch.float32, device=dev)
     buf = st.buffers
+    _mark("zero_fill")
     _capi.check(_lib.gs_blend_bwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if st.k > 0 else None, buf.ptr("records"),
                                   g_img.data_ptr(), st.acc_alpha.data_ptr(), st.last.data_ptr(),
                                   splat_grads.data_ptr(), on_image.data_ptr(), stream),
                 "gs_blend_bwd")
+    _mark("blend_bwd")
     want_hook = hook is not None
     h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None
     h_feat = torch.empty(m, 56, dtype=torch.float32, device=dev) if want_hook else None
@@ -383,6 +401,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
             float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
             grad_pointcloud.data_ptr(), grad_features.data_ptr(), _ptr(h_xyz), _ptr(h_feat),
             _ptr(h_view), _ptr(h_mag), _ptr(h_aff), stream), "gs_point_bwd")
+    _mark("point_bwd")
     if want_hook:
         point_in_camera = buf.view("point_in_camera", m)
         hook(hook_input_type(

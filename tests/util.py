@@ -130,3 +130,12 @@ def grad_error(ref: np.ndarray, got: np.ndarray):
     col[col == 0] = 1.0
     max_norm = float((np.abs(r2 - g2) / col).max()) if r2.size else 0.0
     return rel_l2, max_norm
+
+
+def outlier_fraction(ref: np.ndarray, got: np.ndarray, tol: float) -> float:
+    """Fraction of elements whose error, normalised by the column's max magnitude, exceeds tol."""
+    r2 = np.asarray(ref, np.float64).reshape(ref.shape[0], -1)
+    g2 = np.asarray(got, np.float64).reshape(got.shape[0], -1)
+    col = np.abs(r2).max(axis=0)
+    col[col == 0] = 1.0
+    return float(((np.abs(r2 - g2) / col) > tol).mean()) if r2.size else 0.0
