@@ -1,0 +1,82 @@
+"""View-sharded multi-GPU step (new functionality; the reference is single-GPU, README.md:325).
+
+The path shards over camera views: every rank holds the whole point cloud, renders the views
+`v = rank, rank + world, ...` of a batch forward+backward with the single-view operator, and the one
+exchange step is the sum of the N x 3 + N x 56 gradient over ranks (`all_reduce`, NCCL over NVLink on
+GPUs; gloo in the CPU tests).  One process per GPU, launched with torch.distributed.run.
+
+The operator normalises the quaternion columns of the visible points in place (reference
+R.py:264-266), and different ranks see different points, so the replicas would drift apart by
+rounding in those four columns; `sync_quaternions` re-broadcasts them from rank 0 at the start of a
+step (16 B per point, against 236 B per point for the gradient all-reduce).
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Any, Callable, List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+
+def views_of_rank(num_views: int, rank: int, world: int) -> List[int]:
+    """Indices of the views rank `rank` renders: v = rank (mod world)."""
+    return list(range(rank, num_views, world))
+
+
+@dataclass
+class StepResult:
+    loss: torch.Tensor            # sum of the per-view losses over ALL ranks (scalar)
+    num_local_views: int
+
+
+class ViewShardedTrainerStep:
+    """One data-parallel step over a batch of views.
+
+    render(point_cloud, point_cloud_features, view) -> image  is the single-view operator call
+    (default: none -- pass a closure around GaussianPointCloudRasterisation); loss_fn(image, view)
+    -> scalar.  After `__call__`, `point_cloud.grad` / `point_cloud_features.grad` hold the gradient
+    of the summed loss over every view of the batch, identical on every rank.
+    """
+
+    def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
+                 loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
+                 group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True):
+        self.render = render
+        self.loss_fn = loss_fn
+        self.group = group
+        self.sync_quaternions = sync_quaternions
+
+    def _world(self):
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank(self.group), dist.get_world_size(self.group)
+        return 0, 1
+
+    def __call__(self, point_cloud: torch.Tensor, point_cloud_features: torch.Tensor,
+                 views: Sequence[Any]) -> StepResult:
+        rank, world = self._world()
+        if world > 1 and self.sync_quaternions:
+            with torch.no_grad():
+                q = point_cloud_features.detach()[:, 0:4].contiguous()
+                dist.broadcast(q, src=dist.get_global_rank(self.group, 0) if self.group else 0,
+                               group=self.group)
+                point_cloud_features.detach()[:, 0:4] = q
+        point_cloud.grad = None
+        point_cloud_features.grad = None
+        mine = views_of_rank(len(views), rank, world)
+        total = torch.zeros((), dtype=torch.float32, device=point_cloud.device)
+        for v in mine:
+            image = self.render(point_cloud, point_cloud_features, views[v])
+            loss = self.loss_fn(image, views[v])
+            loss.backward()          # accumulates into .grad across this rank's views
+            total = total + loss.detach()
+        # a rank with no view of this batch still takes part in the exchange with zeros
+        if point_cloud.grad is None:
+            point_cloud.grad = torch.zeros_like(point_cloud)
+        if point_cloud_features.grad is None:
+            point_cloud_features.grad = torch.zeros_like(point_cloud_features)
+        if world > 1:
+            dist.all_reduce(point_cloud.grad, group=self.group)
+            dist.all_reduce(point_cloud_features.grad, group=self.group)
+            dist.all_reduce(total, group=self.group)
+        return StepResult(loss=total, num_local_views=len(mine))
