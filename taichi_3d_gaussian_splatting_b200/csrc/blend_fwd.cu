@@ -4,130 +4,209 @@
 // gso_blend_fwd in oracle/gs_oracle.c operation for operation, so image, depth, accumulated
 // alpha, last-effective index and per-pixel counts are bit-exact with the oracle.
 //
-// One 256-thread CTA per 16x16 tile, one pixel per thread (warp = 2 rows of 16 pixels).  The
-// tile's sorted list is streamed through shared memory in batches of 256 packed 48-byte splat
-// records, double buffered with cp.async so the gather of batch b+1 overlaps the blend of
-// batch b.  A pair whose exponent is below -5.6 cannot reach alpha >= 1/255 (rescale <= 1,
-// opacity <= 1), so it is skipped before the exp -- the same decision the reference makes
-// after it.  The CTA stops as soon as all 256 pixels are saturated (__syncthreads_and); the
-// reference keeps looping without effect (R.py:387-394).
+// The kernel is instruction-issue bound (ncu: issue slots > 90 % busy, DRAM < 10 %), so the design
+// minimises executed warp instructions rather than bytes:
+//
+//   * one WARP owns a column of kCells cells of 8x4 pixels (kCells = 4: an 8x16 half tile,
+//     kCells = 2: an 8x8 quarter tile); lane l owns pixel (l % 8, l / 8) of every cell;
+//   * the tile's sorted list is walked in batches of 32: lane l stages entry l (48-byte record,
+//     three 16-byte loads, prefetched one batch ahead into registers) and computes a kCells-bit
+//     mask -- bit j is set only if the splat can reach alpha >= 1/255 on some pixel centre of
+//     cell j (exact minimum of the conic's quadratic form over every pixel row of the cell, with
+//     a safety margin far above either profile's rounding).  About half of a tile's entries
+//     reach no pixel of the tile at all (bounding-box corners, low opacity), and of the rest
+//     most touch one or two cells;
+//   * the warp then visits only the (entry, cell) combinations whose bit is set and whose cell
+//     still has an unsaturated pixel -- the compositing arithmetic is skipped exactly where the
+//     reference's own `alpha < 1/255` test would have discarded it, so results do not change;
+//   * a cell retires when all its 32 pixels are saturated (one REDUX), the warp stops when all its
+//     cells have retired; the reference keeps looping without effect (R.py:387-394).
+//
+// Warps of one tile share nothing and never synchronise with each other.
+#include <cstdlib>
+
 #include "gs_common.cuh"
 
 namespace {
 
-constexpr int kBatch = 256;
+constexpr int kBatch = 32;
+constexpr int kCellW = 8, kCellH = 4;
 
-__device__ __forceinline__ void cp_async16(void *smem, const void *gmem)
+// Bit j set <=> the splat may reach alpha >= 1/255 at a pixel centre of cell j (rows
+// [4j, 4j+4) of the warp's 8-pixel-wide column).  q(d) = a dx^2 + 2 b dx dy + c dy^2 must stay
+// <= tau = 2 ln(255 * rescale * opacity) there; per pixel row the minimum over the row's centres
+// is taken at dx clamped to the row.  Margin: 0.05 absolute + 4e-6 relative to the positive terms.
+// Conics that are not positive definite / finite keep every bit.
+template <int kCells>
+__device__ __forceinline__ unsigned cell_mask(float u, float v, float a, float b, float c,
+                                              float peak, float x_first, float y_first)
 {
-    unsigned s = (unsigned)__cvta_generic_to_shared(smem);
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(s), "l"(gmem));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait()
-{
-    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+    constexpr unsigned kAll = (1u << kCells) - 1u;
+    if (!(a > 0.0f) || !(c > 0.0f) || !(a * c > b * b) || !isfinite(a + b + c + u + v + peak))
+        return kAll;
+    if (!(peak * 255.0f >= 0.97f)) return 0u;  // alpha <= peak < 1/255 everywhere (e <= 0)
+    const float tau = 2.0f * __logf(peak * 255.0f) + 0.05f;
+    const float inv_a = 1.0f / a;
+    const float lo = x_first - u, hi = lo + (float)(kCellW - 1);
+    unsigned mask = 0u;
+#pragma unroll
+    for (int r = 0; r < kCells * kCellH; ++r) {
+        const float dy = (y_first + (float)r) - v;
+        const float dx = fminf(fmaxf(-b * dy * inv_a, lo), hi);
+        const float pos = a * dx * dx + c * dy * dy;
+        const float q = pos + 2.0f * b * dx * dy;
+        if (q <= tau + 4e-6f * pos) mask |= 1u << (r / kCellH);
+    }
+    return mask;
 }
 
-template <bool kRgbOnly>
-__global__ void __launch_bounds__(kTilePixels)
+template <int kCells, bool kRgbOnly>
+__global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)))
 blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
                  const float4 *__restrict__ records, float *__restrict__ image,
                  float *__restrict__ depth, float *__restrict__ acc_alpha,
                  int32_t *__restrict__ last_effective, int32_t *__restrict__ valid_count)
 {
-    __shared__ float4 s_rec[2][kBatch * 3];
+    constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile
+    constexpr int kPartsPerColumn = kParts / 2;
+    constexpr unsigned kAll = (1u << kCells) - 1u;
+    __shared__ float4 s_rec_all[kParts][kBatch * 3];
 
-    const int tid = threadIdx.x;
+    const int lane = threadIdx.x & 31, part = threadIdx.x >> 5;
+    float4 *s_rec = s_rec_all[part];
     const int tiles_per_row = width / kTile;
     const int tile = blockIdx.x;
     const int tile_u = tile % tiles_per_row, tile_v = tile / tiles_per_row;
-    const int pu = tile_u * kTile + (tid % kTile), pv = tile_v * kTile + (tid / kTile);
-    const float fx = (float)pu + 0.5f, fy = (float)pv + 0.5f;
+    const int col0 = tile_u * kTile + (part / kPartsPerColumn) * kCellW;          // first pixel column
+    const int row0 = tile_v * kTile + (part % kPartsPerColumn) * (kCells * kCellH);  // first pixel row
+    const int pu = col0 + (lane & 7);
+    const int pv0 = row0 + (lane >> 3);
+    const float fx = (float)pu + 0.5f, fy0 = (float)pv0 + 0.5f;
+    const float x_first = (float)col0 + 0.5f, y_first = (float)row0 + 0.5f;
     const int start = tile_start[tile], end = tile_end[tile];
 
-    float T = 1.0f, C0 = 0.f, C1 = 0.f, C2 = 0.f, D = 0.f, Wd = 0.f;
-    int last = start, cnt = 0;
-    bool saturated = false;
+    float T[kCells], C0[kCells], C1[kCells], C2[kCells], D[kCells], Wd[kCells];
+    int last[kCells], cnt[kCells];
+#pragma unroll
+    for (int j = 0; j < kCells; ++j) {
+        T[j] = 1.0f;
+        C0[j] = C1[j] = C2[j] = D[j] = Wd[j] = 0.f;
+        last[j] = start;
+        cnt[j] = 0;
+    }
+    unsigned live = kAll;  // bit j: this lane's pixel of cell j is not saturated yet
+    unsigned open = kAll;  // cells that still have an unsaturated pixel (warp-uniform)
 
-    const int num_batches = (end - start + kBatch - 1) / kBatch;
-    // prologue: stage batch 0
-    if (num_batches > 0) {
-        int i = start + tid;
+    // software pipeline: records of the next batch in registers, payload two batches ahead
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
+    int g_next = 0;
+    {
+        const int i = start + lane;
         if (i < end) {
-            const float4 *src = records + (size_t)3 * payload[i];
-            cp_async16(&s_rec[0][3 * tid], src);
-            cp_async16(&s_rec[0][3 * tid + 1], src + 1);
-            cp_async16(&s_rec[0][3 * tid + 2], src + 2);
+            const float4 *src = records + (size_t)3 * __ldg(payload + i);
+            n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
         }
+        if (i + kBatch < end) g_next = __ldg(payload + i + kBatch);
     }
-    cp_async_commit();
 
-    for (int b = 0; b < num_batches; ++b) {
-        const int buf = b & 1;
-        // stage batch b+1 into the other buffer (its last readers finished before the barrier
-        // that ended iteration b-1)
-        if (b + 1 < num_batches) {
-            int i = start + (b + 1) * kBatch + tid;
+    for (int base = start; base < end && open; base += kBatch) {
+        // ---- stage this batch (registers -> shared) and cull it against the open cells --------
+        unsigned my_mask = 0u;
+        if (base + lane < end)
+            my_mask = open & cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
+        s_rec[3 * lane] = n0;
+        s_rec[3 * lane + 1] = n1;
+        s_rec[3 * lane + 2] = n2;
+        // ---- prefetch the next batch ------------------------------------------------------------
+        {
+            const int i = base + kBatch + lane;
             if (i < end) {
-                const float4 *src = records + (size_t)3 * payload[i];
-                cp_async16(&s_rec[buf ^ 1][3 * tid], src);
-                cp_async16(&s_rec[buf ^ 1][3 * tid + 1], src + 1);
-                cp_async16(&s_rec[buf ^ 1][3 * tid + 2], src + 2);
+                const float4 *src = records + (size_t)3 * g_next;
+                n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
             }
+            if (i + kBatch < end) g_next = __ldg(payload + i + kBatch);
         }
-        cp_async_commit();
-        cp_async_wait<1>();  // batch b has landed (for this thread's copies)
-        __syncthreads();
+        __syncwarp();
 
-        const int base = start + b * kBatch;
-        const int n = min(kBatch, end - base);
-        if (!saturated) {
-            for (int k = 0; k < n; ++k) {
-                const float4 r0 = s_rec[buf][3 * k];      // u v a b
-                const float4 r1 = s_rec[buf][3 * k + 1];  // c rescale alpha red
-                float dx = fx - r0.x, dy = fy - r0.y;
-                float e = -0.5f * (dx * dx * r0.z + dy * dy * r1.x) - dx * dy * r0.w;
-                // exp(-5.6) * 1.0001 < 1/255 and opacity <= 1: same decision as the a < 1/255 test
-                if (e < -5.6f && r1.y <= 1.0001f) continue;
-                float ga = gs_expf(e) * r1.y;
-                float a = ga * r1.z;
-                if (a < 1.0f / 255.0f) continue;
+        unsigned pending = __ballot_sync(0xffffffffu, my_mask != 0u);
+        while (pending) {
+            const int k = __ffs(pending) - 1;
+            pending &= pending - 1u;
+            const unsigned m = __shfl_sync(0xffffffffu, my_mask, k) & open;
+            if (m == 0u) continue;  // warp-uniform
+            const float4 r0 = s_rec[3 * k];      // u v a b
+            const float4 r1 = s_rec[3 * k + 1];  // c rescale alpha red
+            const float4 r2 = s_rec[3 * k + 2];  // green blue z pad
+            const float dx = fx - r0.x;
+            const float dxdxa = dx * dx * r0.z;
+            const int idx1 = base + k + 1;
+#pragma unroll
+            for (int j = 0; j < kCells; ++j) {
+                if (!((m >> j) & 1u)) continue;  // warp-uniform
+                const float dy = (fy0 + (float)(kCellH * j)) - r0.y;
+                const float e = -0.5f * (dxdxa + dy * dy * r1.x) - dx * dy * r0.w;
+                // e < -87 gives alpha < 1/255 with either exp; anything above 88 or NaN is redone
+                // by the guarded version
+                float ex = gs_expf_core(fmaxf(e, -87.0f));
+                if (!(e <= 88.0f)) ex = (e != e) ? e : __int_as_float(0x7f800000);  // as gs_expf
+                float a = ex * r1.y * r1.z;
+                const bool pass = ((live >> j) & 1u) && !(a < 1.0f / 255.0f);
                 a = fminf(a, 0.99f);
-                float nT = T * (1.0f - a);
-                if (nT < 0.0001f) {
-                    saturated = true;
-                    break;
+                const float nT = T[j] * (1.0f - a);
+                const bool sat = pass && (nT < 0.0001f);
+                if (sat) live &= ~(1u << j);
+                if (pass && !sat) {
+                    last[j] = idx1;
+                    C0[j] += r1.w * a * T[j];
+                    C1[j] += r2.x * a * T[j];
+                    C2[j] += r2.y * a * T[j];
+                    if (!kRgbOnly) {
+                        D[j] += r2.z * a * T[j];
+                        Wd[j] += a * T[j];
+                        cnt[j] += 1;
+                    }
+                    T[j] = nT;
                 }
-                const float4 r2 = s_rec[buf][3 * k + 2];  // green blue z pad
-                last = base + k + 1;
-                C0 += r1.w * a * T;
-                C1 += r2.x * a * T;
-                C2 += r2.y * a * T;
-                if (!kRgbOnly) {
-                    D += r2.z * a * T;
-                    Wd += a * T;
-                    cnt += 1;
-                }
-                T = nT;
             }
+            open = __reduce_or_sync(0xffffffffu, live);  // a cell retires with its last live pixel
+            if (open == 0u) break;
         }
-        // everyone is done with buffer `buf`; also the whole-tile early exit
-        if (__syncthreads_and(saturated ? 1 : 0)) break;
+        __syncwarp();
     }
-    cp_async_wait<0>();
 
-    const size_t px = (size_t)pv * width + pu;
-    image[3 * px] = C0;
-    image[3 * px + 1] = C1;
-    image[3 * px + 2] = C2;
-    if (!kRgbOnly) {
-        depth[px] = D / fmaxf(Wd, 1e-6f);
-        acc_alpha[px] = 1.0f - T;
-        last_effective[px] = last;
-        valid_count[px] = cnt;
+#pragma unroll
+    for (int j = 0; j < kCells; ++j) {
+        const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
+        image[3 * px] = C0[j];
+        image[3 * px + 1] = C1[j];
+        image[3 * px + 2] = C2[j];
+        if (!kRgbOnly) {
+            depth[px] = D[j] / fmaxf(Wd[j], 1e-6f);
+            acc_alpha[px] = 1.0f - T[j];
+            last_effective[px] = last[j];
+            valid_count[px] = cnt[j];
+        }
     }
+}
+
+template <int kCells>
+int launch_fwd(int tiles, cudaStream_t st, int rgb_only, int height, int width,
+               const int32_t *tile_start, const int32_t *tile_end, const int32_t *payload,
+               const float4 *rec, float *image, float *depth, float *acc_alpha,
+               int32_t *last_effective, int32_t *valid_count)
+{
+    constexpr int kThreads = 32 * (kTilePixels / (kCells * 32));
+    if (rgb_only)
+        blend_fwd_kernel<kCells, true><<<tiles, kThreads, 0, st>>>(
+            height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
+            last_effective, valid_count);
+    else
+        blend_fwd_kernel<kCells, false><<<tiles, kThreads, 0, st>>>(
+            height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
+            last_effective, valid_count);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
 }
 
 }  // namespace
@@ -142,16 +221,17 @@ extern "C" int gs_blend_fwd(int height, int width, const int32_t *tile_start,
     if (!tile_start || !tile_end || !image) return GS_E_INVALID;
     if (!rgb_only && (!depth || !acc_alpha || !last_effective || !valid_count)) return GS_E_INVALID;
     int tiles = (width / kTile) * (height / kTile);
+    static int cells = 0;
+    if (cells == 0) {
+        const char *e = getenv("GS_FWD_CELLS");  // tuning knob: 8x4 cells per warp (2 or 4)
+        cells = e ? atoi(e) : 4;
+        if (cells != 2 && cells != 4) cells = 4;
+    }
     const float4 *rec = reinterpret_cast<const float4 *>(records);
     cudaStream_t st = (cudaStream_t)stream;
-    if (rgb_only)
-        blend_fwd_kernel<true><<<tiles, kTilePixels, 0, st>>>(height, width, tile_start, tile_end,
-                                                              sorted_payload, rec, image, depth,
-                                                              acc_alpha, last_effective, valid_count);
-    else
-        blend_fwd_kernel<false><<<tiles, kTilePixels, 0, st>>>(height, width, tile_start, tile_end,
-                                                               sorted_payload, rec, image, depth,
-                                                               acc_alpha, last_effective, valid_count);
-    GS_LAUNCH_CHECK();
-    return GS_OK;
+    if (cells == 2)
+        return launch_fwd<2>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload,
+                             rec, image, depth, acc_alpha, last_effective, valid_count);
+    return launch_fwd<4>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload, rec,
+                         image, depth, acc_alpha, last_effective, valid_count);
 }

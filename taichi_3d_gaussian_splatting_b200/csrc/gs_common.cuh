@@ -29,7 +29,8 @@ constexpr int kGradSlots = GS_GRAD_SLOTS;
 __device__ __forceinline__ float gs_expf_core(float x)
 {
     float t = x * 1.44269504088896341f;
-    float j = (t + 12582912.0f) - 12582912.0f;
+    float tj = t + 12582912.0f;  // 1.5 * 2^23: the low mantissa bits of tj hold rint(t)
+    float j = tj - 12582912.0f;
     float f = fmaf(j, -0.693145751953125f, x);
     f = fmaf(j, -1.42860682030941723212e-6f, f);
     float p = 1.9875691500e-4f;
@@ -40,8 +41,8 @@ __device__ __forceinline__ float gs_expf_core(float x)
     p = fmaf(p, f, 5.0000001201e-1f);
     float f2 = f * f;
     float r = fmaf(p, f2, f) + 1.0f;
-    int ji = (int)j;
-    return __int_as_float(__float_as_int(r) + (ji << 23));
+    // (int)j << 23 without the conversion: bits(tj) = 0x4B400000 + j and 0x4B400000 << 23 == 0 (mod 2^32)
+    return __int_as_float(__float_as_int(r) + (__float_as_int(tj) << 23));
 }
 
 __device__ __forceinline__ float gs_expf(float x)
