@@ -114,7 +114,9 @@ int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t
  * Backward blend.  Replaces loop 1 of gaussian_point_rasterisation_backward (R.py:531-705).
  * splat_grads [m, 12] f32 must be zero on entry; per visible point it receives
  *   0:duv.u 1:duv.v 2:dcov00 3:dcov01 4:dcov11 5:dr 6:dg 7:db 8:dlogit 9:|duv| 10:#pixels(as float) 11:0
- * map_on_image [H,W,2] gets the per-pixel sum of |duv| (R.py:700-704).
+ * map_on_image [H,W,2] gets the per-pixel sum of |duv| (R.py:700-704).  It may be null: the
+ * magnitudes (the map and slot 9) are observable only through the reference's backward hook, and
+ * a caller without one skips them (slot 9 then stays 0).
  */
 int gs_blend_bwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
                  const int32_t *sorted_payload, const float *records, const float *image_grad,

@@ -374,17 +374,19 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     if grad_rasterized_image is None:
         grad_rasterized_image = torch.zeros(H, W, 3, dtype=torch.float32, device=dev)
     g_img = grad_rasterized_image.detach().to(torch.float32).contiguous()
-    on_image = torch.empty(H, W, 2, dtype=torch.float32, device=dev)
+    want_hook = hook is not None
+    # |d uv| magnitudes (R.py:700-704) are visible only through the hook; without one the kernel
+    # skips them (map_on_image = NULL)
+    on_image = torch.empty(H, W, 2, dtype=torch.float32, device=dev) if want_hook else None
     splat_grads = torch.zeros(max(m, 1), _GRAD_SLOTS, dtype=torch.float32, device=dev)
     buf = st.buffers
     _mark("zero_fill")
     _capi.check(_lib.gs_blend_bwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if st.k > 0 else None, buf.ptr("records"),
                                   g_img.data_ptr(), st.acc_alpha.data_ptr(), st.last.data_ptr(),
-                                  splat_grads.data_ptr(), on_image.data_ptr(), stream),
+                                  splat_grads.data_ptr(), _ptr(on_image), stream),
                 "gs_blend_bwd")
     _mark("blend_bwd")
-    want_hook = hook is not None
     h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None
     h_feat = torch.empty(m, 56, dtype=torch.float32, device=dev) if want_hook else None
     h_view = torch.empty(m, 2, dtype=torch.float32, device=dev) if want_hook else None
@@ -416,8 +418,6 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
             point_depth=point_in_camera[:, 2],
             point_uv_in_camera=buf.view("point_uv", m),
         ))
-    st.info["magnitude_grad_viewspace_on_image"] = on_image
-    st.info["splat_grads"] = splat_grads
     return grad_pointcloud, grad_features
 
 

@@ -1,21 +1,25 @@
 // blend_bwd.cu -- reverse-order blend backward (reference R.py:531-705, utils.py:331-348).
 //
-// Fast-fp32 profile (FMA contraction, ex2.approx): gradients are compared with the oracle at
-// 1e-4 relative, the atomic summation order differs from the reference anyway.
+// Fast-fp32 profile (FMA contraction, ex2.approx, rcp.approx): gradients are compared with the
+// oracle at 1e-4 relative, the atomic summation order differs from the reference anyway.
 //
-// One WARP per 16x16 tile; lane l owns the 8 pixels (x = l % 16, y = 2 j + l / 16), j = 0..7
-// ("slot" j = the 16x2 pixel strip of rows 2j, 2j+1).  The tile's list is walked from
-// max-over-pixels(last effective index) down to the tile start (entries past that maximum are
-// skipped by every pixel in the reference too, R.py:609-610) in batches of 32: lane l stages
-// entry l of the batch and computes an 8-bit slot mask for it -- bit j is set only if the splat
-// can reach alpha >= 1/255 on some pixel centre of strip j (exact minimum of the conic's
-// quadratic form over each pixel row, with a safety margin) and some pixel of the strip still
-// has that entry before its last effective index.  The warp then visits only (splat, strip)
-// combinations whose bit is set, sums the 10 per-pixel gradient terms over the strips in
-// registers, and reduces them across the warp once per (tile, splat) with a recursive-halving
-// butterfly (16 shuffles), followed by three 16-byte vector reductions into the [M,12]
-// splat-gradient buffer.  The reference issues 11 global atomics per (pixel, splat) pair
-// (R.py:674-696).
+// Instruction-issue bound like the forward blend, and laid out the same way: one WARP owns a
+// column of kCells cells of 8x4 pixels (kCells = 4: an 8x16 half tile); lane l owns pixel
+// (l % 8, l / 8) of every cell.  The tile's list is walked from max-over-pixels(last effective
+// index) down to the tile start (entries past that maximum are skipped by every pixel in the
+// reference too, R.py:609-610) in batches of 32: lane l stages entry l of the batch (records
+// prefetched one batch ahead into registers) and computes a kCells-bit mask -- bit j is set only
+// if the splat can reach alpha >= 1/255 on some pixel centre of cell j (gs_cell_mask) and some
+// pixel of the cell still has that entry before its last effective index.  The warp then visits
+// only (entry, cell) combinations whose bit is set, sums the per-pixel gradient terms over its
+// cells in registers, and reduces them across the warp once per (warp, entry) with a
+// recursive-halving butterfly over 10 values (12 shuffles), followed by three 16-byte vector
+// reductions into the [M,12] splat-gradient buffer.  The reference issues 11 global atomics per
+// (pixel, splat) pair (R.py:674-696).
+//
+// Per pixel the three colour channels are folded: with cg = colour . dL/dpixel, the reference's
+// sum_c (colour_c T - w_c / (1 - alpha)) dL/dpixel_c equals T cg - wg / (1 - alpha), where
+// wg = sum over the entries behind of (alpha T) cg, so one accumulator replaces three.
 #include <cstdlib>
 
 #include "gs_common.cuh"
@@ -51,224 +55,242 @@ __device__ __forceinline__ float fast_sqrt(float x)
     return y;
 }
 
-// Sum 16 per-lane values over the 32 lanes of a warp.  On return lane L holds in v[0] the total
-// of value index L >> 1.
-__device__ __forceinline__ void warp_reduce16(float (&v)[16], int lane)
+// Sum 10 per-lane values over the 32 lanes of a warp with 12 shuffles.  On return v[0] of lane L
+// holds the total of value index q = 5 b4 + 3 b3 + 2 b2 + b1 (b_i = bit i of L) when
+// (b3, b2, b1) is one of 000 001 010 100 101, and padding otherwise; see reduced_slot().
+__device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane)
 {
     {
-        const bool up = lane & 16;
+        const bool up = lane & 16;  // 10 -> 5: lower lanes keep 0..4, upper lanes keep 5..9
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float send = up ? v[i] : v[i + 8];
-            float keep = up ? v[i + 8] : v[i];
+        for (int i = 0; i < 5; ++i) {
+            const float send = up ? v[i] : v[i + 5];
+            const float keep = up ? v[i + 5] : v[i];
             v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
         }
     }
     {
-        const bool up = lane & 8;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            float send = up ? v[i] : v[i + 4];
-            float keep = up ? v[i + 4] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
-        }
+        const bool up = lane & 8;  // 5 -> 3: lower keep x0 x1 x2, upper keep x3 x4 (pad)
+        const float s0 = up ? v[0] : v[3], k0 = up ? v[3] : v[0];
+        const float s1 = up ? v[1] : v[4], k1 = up ? v[4] : v[1];
+        const float s2 = up ? v[2] : 0.0f, k2 = up ? 0.0f : v[2];
+        v[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 8);
+        v[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 8);
+        v[2] = k2 + __shfl_xor_sync(0xffffffffu, s2, 8);
     }
     {
-        const bool up = lane & 4;
-#pragma unroll
-        for (int i = 0; i < 2; ++i) {
-            float send = up ? v[i] : v[i + 2];
-            float keep = up ? v[i + 2] : v[i];
-            v[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
-        }
+        const bool up = lane & 4;  // 3 -> 2: lower keep y0 y1, upper keep y2 (pad)
+        const float s0 = up ? v[0] : v[2], k0 = up ? v[2] : v[0];
+        const float s1 = up ? v[1] : 0.0f, k1 = up ? 0.0f : v[1];
+        v[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 4);
+        v[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 4);
     }
     {
-        const bool up = lane & 2;
-        float send = up ? v[0] : v[1];
-        float keep = up ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+        const bool up = lane & 2;  // 2 -> 1
+        const float s0 = up ? v[0] : v[1], k0 = up ? v[1] : v[0];
+        v[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 2);
     }
     v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
-// Bit j set <=> the splat may reach alpha >= 1/255 at a pixel centre of strip j of this tile.
-// q(d) = a dx^2 + 2 b dx dy + c dy^2 must stay <= tau = 2 ln(255 * rescale * alpha) there; per
-// pixel row the minimum over the row's 16 centres is taken at dx clamped to the row, so the test
-// is exact up to the margin (0.05 absolute + 4e-6 relative to the positive terms, far above the
-// rounding of either arithmetic profile).  Degenerate conics keep every bit.
-template <int kRows>
-__device__ __forceinline__ unsigned strip_mask(float u, float v, float a, float b, float c,
-                                               float opacity, float x_first, float y_first)
+// value index held by lane L after warp_reduce10, or -1 for padding / duplicate lanes
+__device__ __forceinline__ int reduced_slot(int lane)
 {
-    if (!(opacity * 255.0f >= 0.97f)) return 0u;         // alpha <= rescale*alpha < 1/255 everywhere
-    if (!(a > 0.0f) || !(c > 0.0f) || !isfinite(a + b + c + u + v)) return (1u << (kRows / 2)) - 1u;
-    const float tau = 2.0f * __logf(opacity * 255.0f) + 0.05f;
-    const float inv_a = 1.0f / a;
-    const float lo = x_first - u, hi = lo + 15.0f;
-    unsigned mask = 0u;
-#pragma unroll
-    for (int r = 0; r < kRows; ++r) {
-        const float dy = (y_first + (float)r) - v;
-        const float dx = fminf(fmaxf(-b * dy * inv_a, lo), hi);
-        const float pos = a * dx * dx + c * dy * dy;
-        const float q = pos + 2.0f * b * dx * dy;
-        if (q <= tau + 4e-6f * pos) mask |= 1u << (r >> 1);
-    }
-    return mask;
+    if (lane & 1) return -1;
+    const int b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1;
+    if (b2 && (b1 || b3)) return -1;
+    return 5 * (lane >> 4) + 3 * b3 + 2 * b2 + b1;
 }
 
-// kSlots strips (2 kSlots pixel rows) of one tile per warp: 8 = whole tile, 4 = half, 2 = quarter.
-template <int kSlots>
-__global__ void __launch_bounds__(32)
+template <int kCells, bool kMagnitude>
+__global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)))
 blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
                  const float4 *__restrict__ records, const float *__restrict__ image_grad,
                  const float *__restrict__ acc_alpha, const int32_t *__restrict__ last_effective,
                  float *__restrict__ splat_grads, float *__restrict__ map_on_image)
 {
-    __shared__ float4 s_rec[kBatch * 3];
-    __shared__ __align__(16) float s_out[kBatch * kGradSlots];
-    __shared__ unsigned s_mask[kBatch];
+    constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile
+    constexpr int kPartsPerColumn = kParts / 2;
+    __shared__ float4 s_rec_all[kParts][kBatch * 3];
+    __shared__ __align__(16) float s_out_all[kParts][kBatch * kGradSlots];
 
-    const int lane = threadIdx.x;
+    const int lane = threadIdx.x & 31, part = threadIdx.x >> 5;
+    float4 *s_rec = s_rec_all[part];
+    float *s_out = s_out_all[part];
     const int tiles_per_row = width / kTile;
-    constexpr int kParts = 8 / kSlots;  // warps (CTAs) per tile
-    const int tile = blockIdx.x / kParts, part = blockIdx.x % kParts;
+    const int tile = blockIdx.x;
     const int tile_u = tile % tiles_per_row, tile_v = tile / tiles_per_row;
-    const int row0 = tile_v * kTile + part * (2 * kSlots);  // first pixel row of this warp
-    const int pu = tile_u * kTile + (lane & 15);
-    const int pv0 = row0 + (lane >> 4);
+    const int col0 = tile_u * kTile + (part / kPartsPerColumn) * kCellW;
+    const int row0 = tile_v * kTile + (part % kPartsPerColumn) * (kCells * kCellH);
+    const int pu = col0 + (lane & 7);
+    const int pv0 = row0 + (lane >> 3);
     const float fx = (float)pu + 0.5f, fy0 = (float)pv0 + 0.5f;
-    const float x_first = (float)(tile_u * kTile) + 0.5f, y_first = (float)row0 + 0.5f;
+    const float x_first = (float)col0 + 0.5f, y_first = (float)row0 + 0.5f;
     const int start = tile_start[tile], end = tile_end[tile];
 
-    float T[kSlots], w0[kSlots], w1[kSlots], w2[kSlots], g0[kSlots], g1[kSlots], g2[kSlots];
-    float tot0[kSlots], tot1[kSlots];
-    int last[kSlots], slot_last[kSlots];
+    float T[kCells], wg[kCells], g0[kCells], g1[kCells], g2[kCells];
+    float tot0[kCells], tot1[kCells];
+    int last[kCells], cell_last[kCells];
     int hi = start;
 #pragma unroll
-    for (int j = 0; j < kSlots; ++j) {
-        const size_t px = (size_t)(pv0 + 2 * j) * width + pu;
+    for (int j = 0; j < kCells; ++j) {
+        const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
         last[j] = (end > start) ? min(last_effective[px], end) : start;
         T[j] = 1.0f - acc_alpha[px];
         g0[j] = image_grad[3 * px];
         g1[j] = image_grad[3 * px + 1];
         g2[j] = image_grad[3 * px + 2];
-        w0[j] = w1[j] = w2[j] = tot0[j] = tot1[j] = 0.f;
-        slot_last[j] = __reduce_max_sync(0xffffffffu, last[j]);
-        hi = max(hi, slot_last[j]);
+        wg[j] = tot0[j] = tot1[j] = 0.f;
+        cell_last[j] = __reduce_max_sync(0xffffffffu, last[j]);
+        hi = max(hi, cell_last[j]);
+    }
+    const int my_slot = reduced_slot(lane);
+
+    // software pipeline: records of the next batch in registers, payload two batches ahead
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
+    int g_cur = 0, g_next = 0;
+    {
+        const int i = hi - 1 - lane;
+        if (i >= start) {
+            g_cur = __ldg(payload + i);
+            const float4 *src = records + (size_t)3 * g_cur;
+            n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
+        }
+        if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
     }
 
     for (int top = hi; top > start; top -= kBatch) {
-        const int n = min(kBatch, top - start);
-        // ---- stage: lane l takes entry top-1-l (reverse order) ------------------------------
-        int my_g = 0;
+        // ---- stage: lane l holds entry top-1-l (reverse order) ---------------------------------
+        const int my_i = top - 1 - lane;
+        const int my_g = g_cur;
         unsigned my_mask = 0u;
-        if (lane < n) {
-            const int i = top - 1 - lane;
-            my_g = payload[i];
-            const float4 *src = records + (size_t)3 * my_g;
-            const float4 r0 = __ldg(src), r1 = __ldg(src + 1), r2 = __ldg(src + 2);
-            s_rec[3 * lane] = r0;
-            s_rec[3 * lane + 1] = r1;
-            s_rec[3 * lane + 2] = r2;
+        if (my_i >= start) {
             unsigned live = 0u;
 #pragma unroll
-            for (int j = 0; j < kSlots; ++j) live |= (i < slot_last[j] ? 1u : 0u) << j;
-            my_mask = live ? (live & strip_mask<2 * kSlots>(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y * r1.z, x_first,
-                                                y_first))
-                           : 0u;
+            for (int j = 0; j < kCells; ++j) live |= (my_i < cell_last[j] ? 1u : 0u) << j;
+            if (live)
+                my_mask = live & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z,
+                                                      x_first, y_first);
         }
-        s_mask[lane] = my_mask;
+        s_rec[3 * lane] = n0;
+        s_rec[3 * lane + 1] = n1;
+        s_rec[3 * lane + 2] = n2;
         s_out[kGradSlots * lane + 10] = 0.f;
+        // ---- prefetch the next batch -----------------------------------------------------------
+        {
+            const int i = my_i - kBatch;
+            g_cur = g_next;
+            if (i >= start) {
+                const float4 *src = records + (size_t)3 * g_cur;
+                n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
+            }
+            if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
+        }
         __syncwarp();
 
-        for (int k = 0; k < n; ++k) {
-            const unsigned m = s_mask[k];
-            if (m == 0u) continue;  // warp-uniform
+        unsigned pending = __ballot_sync(0xffffffffu, my_mask != 0u);
+        while (pending) {
+            const int k = __ffs(pending) - 1;
+            pending &= pending - 1u;
+            const unsigned m = __shfl_sync(0xffffffffu, my_mask, k);
             const int i = top - 1 - k;
             const float4 r0 = s_rec[3 * k];      // u v a b
             const float4 r1 = s_rec[3 * k + 1];  // c rescale alpha red
             const float4 r2 = s_rec[3 * k + 2];  // green blue z pad
             const float dx = fx - r0.x;
             const float adx = r0.z * dx, bdx = r0.w * dx;
-            float v[16];
+            const float peak = r1.y * r1.z;
+            float v[10];
 #pragma unroll
-            for (int q = 0; q < 16; ++q) v[q] = 0.f;
-            int count = 0;
+            for (int q = 0; q < 10; ++q) v[q] = 0.f;
+            int hits = 0;
 #pragma unroll
-            for (int j = 0; j < kSlots; ++j) {
+            for (int j = 0; j < kCells; ++j) {
                 if (!((m >> j) & 1u)) continue;  // warp-uniform
-                const float dy = (fy0 + (float)(2 * j)) - r0.y;
-                const float v0 = adx + r0.w * dy;
-                const float v1 = bdx + r1.x * dy;
-                const float quad = dx * v0 + dy * v1;
-                const float p = fast_ex2(-0.72134752044448170368f * quad) * r1.y;  // exp(-quad/2)
-                const float prod = p * r1.z;
-                const bool contributes = (i < last[j]) && (prod >= 1.0f / 255.0f);
-                count += __popc(__ballot_sync(0xffffffffu, contributes));
-                if (contributes) {
+                const float dy = (fy0 + (float)(kCellH * j)) - r0.y;
+                const float v0 = fmaf(r0.w, dy, adx);
+                const float v1 = fmaf(r1.x, dy, bdx);
+                const float quad = fmaf(dy, v1, dx * v0);
+                const float prod = fast_ex2(-0.72134752044448170368f * quad) * peak;  // alpha
+                if ((i < last[j]) && (prod >= 1.0f / 255.0f)) {
+                    hits += 1;
                     const float a = fminf(prod, 0.99f);
                     const float inv = fast_rcp(1.0f - a);
                     const float Tn = T[j] * inv;
                     T[j] = Tn;
                     const float dcol = a * Tn;
-                    const float agr = (r1.w * Tn - w0[j] * inv) * g0[j] +
-                                      (r2.x * Tn - w1[j] * inv) * g1[j] +
-                                      (r2.y * Tn - w2[j] * inv) * g2[j];
-                    w0[j] += r1.w * dcol;
-                    w1[j] += r2.x * dcol;
-                    w2[j] += r2.y * dcol;
-                    const float sa = agr * prod;  // dL/dp * p
+                    const float cg = fmaf(r2.y, g2[j], fmaf(r2.x, g1[j], r1.w * g0[j]));
+                    const float sa = (Tn * cg - inv * wg[j]) * prod;  // dL/dalpha * alpha
+                    wg[j] = fmaf(dcol, cg, wg[j]);
                     const float gm0 = sa * v0, gm1 = sa * v1;
-                    tot0[j] += fabsf(gm0);
-                    tot1[j] += fabsf(gm1);
-                    const float hs = 0.5f * sa;
                     v[0] += gm0;
                     v[1] += gm1;
-                    v[2] += hs * v0 * v0;
-                    v[3] += hs * v0 * v1;
-                    v[4] += hs * v1 * v1;
-                    v[5] += dcol * g0[j];
-                    v[6] += dcol * g1[j];
-                    v[7] += dcol * g2[j];
+                    v[2] = fmaf(gm0, v0, v[2]);
+                    v[3] = fmaf(gm0, v1, v[3]);
+                    v[4] = fmaf(gm1, v1, v[4]);
+                    v[5] = fmaf(dcol, g0[j], v[5]);
+                    v[6] = fmaf(dcol, g1[j], v[6]);
+                    v[7] = fmaf(dcol, g2[j], v[7]);
                     v[8] += sa;
-                    v[9] += fast_sqrt(gm0 * gm0 + gm1 * gm1);
+                    if (kMagnitude) {
+                        tot0[j] += fabsf(gm0);
+                        tot1[j] += fabsf(gm1);
+                        v[9] += fast_sqrt(fmaf(gm0, gm0, gm1 * gm1));
+                    }
                 }
             }
+            const int count = __reduce_add_sync(0xffffffffu, hits);
             if (count == 0) continue;  // warp-uniform
-            v[8] *= (1.0f - r1.z);     // dlogit = sum(sa) * (1 - opacity)
-            warp_reduce16(v, lane);
-            const int q = lane >> 1;
-            if (!(lane & 1)) {
-                if (q < 10)
-                    s_out[kGradSlots * k + q] = v[0];
-                else if (q == 10)
-                    s_out[kGradSlots * k + 10] = (float)count;
-            }
+            v[2] *= 0.5f;
+            v[3] *= 0.5f;
+            v[4] *= 0.5f;
+            v[8] *= (1.0f - r1.z);  // dlogit = sum(sa) * (1 - opacity)
+            warp_reduce10(v, lane);
+            if (my_slot >= 0) s_out[kGradSlots * k + my_slot] = v[0];
+            if (lane == 1) s_out[kGradSlots * k + 10] = (float)count;
         }
         __syncwarp();
         // ---- flush: lane l owns entry l of the batch ------------------------------------------
-        if (lane < n && my_mask != 0u) {
+        if (my_mask != 0u) {
             const float4 *acc = reinterpret_cast<const float4 *>(s_out) + (kGradSlots / 4) * lane;
             const float4 a2 = acc[2];
-            if (a2.z > 0.f) {  // at least one pixel of this tile touched the splat
+            if (a2.z > 0.f) {  // at least one pixel of this warp touched the splat
                 const float4 a0 = acc[0], a1 = acc[1];
                 float *dst = splat_grads + (size_t)kGradSlots * my_g;
                 red_add_v4(dst, a0.x, a0.y, a0.z, a0.w);
                 red_add_v4(dst + 4, a1.x, a1.y, a1.z, a1.w);
-                red_add_v4(dst + 8, a2.x, a2.y, a2.z, 0.f);
+                red_add_v4(dst + 8, a2.x, kMagnitude ? a2.y : 0.f, a2.z, 0.f);
             }
         }
         __syncwarp();
     }
-    if (map_on_image) {
+    if (kMagnitude) {
 #pragma unroll
-        for (int j = 0; j < kSlots; ++j) {
-            const size_t px = (size_t)(pv0 + 2 * j) * width + pu;
+        for (int j = 0; j < kCells; ++j) {
+            const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
             reinterpret_cast<float2 *>(map_on_image)[px] = make_float2(tot0[j], tot1[j]);
         }
     }
+}
+
+template <int kCells>
+int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t *tile_start,
+               const int32_t *tile_end, const int32_t *payload, const float4 *rec,
+               const float *image_grad, const float *acc_alpha, const int32_t *last_effective,
+               float *splat_grads, float *map_on_image)
+{
+    constexpr int kThreads = 32 * (kTilePixels / (kCells * 32));
+    if (map_on_image)
+        blend_bwd_kernel<kCells, true><<<tiles, kThreads, 0, st>>>(
+            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,
+            splat_grads, map_on_image);
+    else
+        blend_bwd_kernel<kCells, false><<<tiles, kThreads, 0, st>>>(
+            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,
+            splat_grads, map_on_image);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
 }
 
 }  // namespace
@@ -280,28 +302,20 @@ extern "C" int gs_blend_bwd(int height, int width, const int32_t *tile_start,
                             void *stream)
 {
     if (height <= 0 || width <= 0 || height % kTile || width % kTile) return GS_E_INVALID;
-    if (!tile_start || !tile_end || !image_grad || !acc_alpha || !last_effective) return GS_E_INVALID;
+    if (!tile_start || !tile_end || !image_grad || !acc_alpha || !last_effective || !splat_grads)
+        return GS_E_INVALID;
     int tiles = (width / kTile) * (height / kTile);
-    static int slots = 0;
-    if (slots == 0) {
-        const char *e = getenv("GS_BWD_SLOTS");  // tuning knob: strips per warp (2, 4 or 8)
-        slots = e ? atoi(e) : 4;
-        if (slots != 2 && slots != 4 && slots != 8) slots = 4;
+    static int cells = 0;
+    if (cells == 0) {
+        const char *e = getenv("GS_BWD_CELLS");  // tuning knob: 8x4 cells per warp (2 or 4)
+        cells = e ? atoi(e) : 4;
+        if (cells != 2 && cells != 4) cells = 4;
     }
     const float4 *rec = reinterpret_cast<const float4 *>(records);
     cudaStream_t st = (cudaStream_t)stream;
-    if (slots == 8)
-        blend_bwd_kernel<8><<<tiles, 32, 0, st>>>(height, width, tile_start, tile_end, sorted_payload, rec,
-                                                  image_grad, acc_alpha, last_effective, splat_grads,
-                                                  map_on_image);
-    else if (slots == 4)
-        blend_bwd_kernel<4><<<tiles * 2, 32, 0, st>>>(height, width, tile_start, tile_end, sorted_payload,
-                                                      rec, image_grad, acc_alpha, last_effective,
-                                                      splat_grads, map_on_image);
-    else
-        blend_bwd_kernel<2><<<tiles * 4, 32, 0, st>>>(height, width, tile_start, tile_end, sorted_payload,
-                                                      rec, image_grad, acc_alpha, last_effective,
-                                                      splat_grads, map_on_image);
-    GS_LAUNCH_CHECK();
-    return GS_OK;
+    if (cells == 2)
+        return launch_bwd<2>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
+                             image_grad, acc_alpha, last_effective, splat_grads, map_on_image);
+    return launch_bwd<4>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
+                         image_grad, acc_alpha, last_effective, splat_grads, map_on_image);
 }

@@ -30,36 +30,6 @@
 namespace {
 
 constexpr int kBatch = 32;
-constexpr int kCellW = 8, kCellH = 4;
-
-// Bit j set <=> the splat may reach alpha >= 1/255 at a pixel centre of cell j (rows
-// [4j, 4j+4) of the warp's 8-pixel-wide column).  q(d) = a dx^2 + 2 b dx dy + c dy^2 must stay
-// <= tau = 2 ln(255 * rescale * opacity) there; per pixel row the minimum over the row's centres
-// is taken at dx clamped to the row.  Margin: 0.05 absolute + 4e-6 relative to the positive terms.
-// Conics that are not positive definite / finite keep every bit.
-template <int kCells>
-__device__ __forceinline__ unsigned cell_mask(float u, float v, float a, float b, float c,
-                                              float peak, float x_first, float y_first)
-{
-    constexpr unsigned kAll = (1u << kCells) - 1u;
-    if (!(a > 0.0f) || !(c > 0.0f) || !(a * c > b * b) || !isfinite(a + b + c + u + v + peak))
-        return kAll;
-    if (!(peak * 255.0f >= 0.97f)) return 0u;  // alpha <= peak < 1/255 everywhere (e <= 0)
-    const float tau = 2.0f * __logf(peak * 255.0f) + 0.05f;
-    const float inv_a = 1.0f / a;
-    const float lo = x_first - u, hi = lo + (float)(kCellW - 1);
-    unsigned mask = 0u;
-#pragma unroll
-    for (int r = 0; r < kCells * kCellH; ++r) {
-        const float dy = (y_first + (float)r) - v;
-        const float dx = fminf(fmaxf(-b * dy * inv_a, lo), hi);
-        const float pos = a * dx * dx + c * dy * dy;
-        const float q = pos + 2.0f * b * dx * dy;
-        if (q <= tau + 4e-6f * pos) mask |= 1u << (r / kCellH);
-    }
-    return mask;
-}
-
 template <int kCells, bool kRgbOnly>
 __global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)))
 blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
@@ -114,7 +84,7 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         // ---- stage this batch (registers -> shared) and cull it against the open cells --------
         unsigned my_mask = 0u;
         if (base + lane < end)
-            my_mask = open & cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
+            my_mask = open & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
         s_rec[3 * lane] = n0;
         s_rec[3 * lane + 1] = n1;
         s_rec[3 * lane + 2] = n2;

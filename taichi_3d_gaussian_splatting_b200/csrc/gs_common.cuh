@@ -90,6 +90,40 @@ __device__ __forceinline__ void gs_sh_basis(float dx, float dy, float dz, float 
     b[15] = (float)0.59004358992664352 * x * (-x * x + 3.0f * y * y);
 }
 
+// ---- per-cell culling shared by the two blend kernels --------------------------------------------
+// A warp owns a column of kCells cells of 8x4 pixels.  Bit j of the result is set <=> the splat
+// may reach alpha >= 1/255 at a pixel centre of cell j (rows [4j, 4j+4) of the column, first
+// pixel centre (x_first, y_first)).  q(d) = a dx^2 + 2 b dx dy + c dy^2 must stay <= tau =
+// 2 ln(255 * peak), peak = rescale * opacity, there; per pixel row the minimum over the row's 8
+// centres is taken at dx clamped to the row, so the test is exact up to the margin (0.05 absolute
+// + 4e-6 relative to the positive terms, far above the rounding of either arithmetic profile).
+// Conics that are not positive definite / finite keep every bit.
+constexpr int kCellW = 8, kCellH = 4;
+
+template <int kCells>
+__device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, float b, float c,
+                                                 float peak, float x_first, float y_first)
+{
+    constexpr unsigned kAll = (1u << kCells) - 1u;
+    if (!(a > 0.0f) || !(c > 0.0f) || !(a * c > b * b) || !isfinite(a + b + c + u + v + peak))
+        return kAll;
+    if (!(peak * 255.0f >= 0.97f)) return 0u;  // alpha <= peak < 1/255 everywhere (e <= 0)
+    const float tau = fmaf(2.0f, __logf(peak * 255.0f), 0.05f);
+    const float slope = -b / a;  // unconstrained minimiser of a row: dx = slope * dy
+    const float lo = x_first - u, hi = lo + (float)(kCellW - 1);
+    const float b2 = 2.0f * b;
+    unsigned mask = 0u;
+#pragma unroll
+    for (int r = 0; r < kCells * kCellH; ++r) {
+        const float dy = (y_first + (float)r) - v;
+        const float dx = fminf(fmaxf(slope * dy, lo), hi);
+        const float pos = fmaf(a * dx, dx, (c * dy) * dy);
+        const float q = fmaf(b2 * dx, dy, pos);
+        if (q <= fmaf(4e-6f, pos, tau)) mask |= 1u << (r / kCellH);
+    }
+    return mask;
+}
+
 __device__ __forceinline__ unsigned long long gs_ld_volatile_u64(const unsigned long long *p)
 {
     return *reinterpret_cast<const volatile unsigned long long *>(p);
