@@ -127,13 +127,28 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def stage_bytes(n, m, k, tiles, hw, passes):
+def stage_bytes(n, m, k, tiles, hw, info):
     """ALGORITHMIC bytes per call of each stage (stated in DESIGN.md)."""
+    depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
+    if info.get("key_pipeline") == "depth_first":
+        pm, pk = (depth_bits + 7) // 8, (tile_bits + 7) // 8
+        keys = {
+            # argsort of M 4-byte depth keys: histogram read + per pass key/value read and write
+            "sort_points": m * (4 + 16 * pm - 4),
+            "emit_keys": 12 * m + 8 * k,            # order + bbox in, tile id + payload out
+            "sort_pairs": k * (4 + 16 * pk),         # histogram read + per pass 8 B in, 8 B out
+            "tile_ranges": 4 * k + 8 * tiles,
+        }
+    else:
+        passes = (depth_bits + tile_bits + 7) // 8
+        keys = {
+            "emit_keys": 24 * m + 12 * k,
+            "sort_pairs": k * (8 + 24 * passes),
+            "tile_ranges": 8 * k + 8 * tiles,
+        }
     return {
         "project_cull_sh": 17 * n + 296 * m,
-        "emit_keys": 24 * m + 12 * k,
-        "sort_pairs": k * (8 + 24 * passes),
-        "tile_ranges": 8 * k + 8 * tiles,
+        **keys,
         "blend_fwd": 48 * k + 28 * hw,
         "zero_fill": 4 * 59 * n + 48 * m,
         "blend_bwd": 44 * k + 28 * hw + 8 * hw + 44 * m,
@@ -324,7 +339,6 @@ def run_b200(args):
 
     info = ras.last_forward_info
     m, k = int(info["num_points_in_camera"]), int(info["num_keys"])
-    passes = (int(info["depth_bits"]) + int(info["tile_bits"]) + 7) // 8
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -332,7 +346,7 @@ def run_b200(args):
 
     tiles, hw = (w // 16) * (h // 16), w * h
     hbm_peak, peak_src = peaks()
-    sbytes = stage_bytes(n, m, k, tiles, hw, passes)
+    sbytes = stage_bytes(n, m, k, tiles, hw, info)
     stages = {}
     for name, rec in stage_ms.items():
         per_call = rec["ms"] / max(rec["calls"], 1)
@@ -375,8 +389,13 @@ def run_b200(args):
                             alt_peak=round(FP32_PEAK_TFLOPS, 1), alt_unit="TFLOP/s",
                             alt_frac=d["fp32_frac"])
 
-    launches_per_step = 1 + 1 + 1 + 2 + passes + 1 + 1 + 1 + 1  # pose, project, emit, hist+scan,
-    #                     onesweep passes, ranges, blend_fwd, blend_bwd, point_bwd
+    depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
+    if info.get("key_pipeline") == "depth_first":
+        # pose, project | point sort: hist+scan+passes | emit | pair sort: hist+scan+passes |
+        # ranges, blend_fwd, blend_bwd, point_bwd
+        launches_per_step = 2 + (2 + (depth_bits + 7) // 8) + 1 + (2 + (tile_bits + 7) // 8) + 4
+    else:
+        launches_per_step = 2 + 1 + (2 + (depth_bits + tile_bits + 7) // 8) + 4
     h2d = wt_host.numel() * 4 + 16 + 12
     line = {
         "metric": METRIC, "value": world * args.steps / (ms_resident * 1e-3), "unit": "it/s",
@@ -386,6 +405,7 @@ def run_b200(args):
         "config": {"workload": args.workload, "points": n, "width": w, "height": h, "sh_degree": 3,
                    "near": 0.8, "far": 1000.0, "depth_to_sort_key_scale": 100.0,
                    "visible_points": m, "keys": k, "views": NUM_VIEWS,
+                   "key_pipeline": info.get("key_pipeline"),
                    "parallelism": f"views sharded over {world} rank(s), replicated cloud"
                                   + (", NCCL all-reduce of the Nx59 gradient per step" if world > 1 else ""),
                    "l2": "inputs exceed L2 (236 MB of point data read per step)"},

@@ -40,9 +40,11 @@ int gs_abi_version(void);
 /* Human-readable text for a status returned by any entry point (static storage). */
 const char *gs_status_string(int status);
 
-/* Bytes of scratch `workspace` the forward needs for n points / k_capacity keys. */
+/* Bytes of scratch `workspace` the forward needs for n points / m visible points / k keys. */
 int64_t gs_project_workspace_bytes(int64_t n);
-int64_t gs_sort_workspace_bytes(int64_t k);
+int64_t gs_sort_workspace_bytes(int64_t k);        /* gs_sort_pairs and gs_sort_pairs32 */
+int64_t gs_point_sort_workspace_bytes(int64_t m);  /* gs_sort_points_by_depth */
+int64_t gs_emit_workspace_bytes(int64_t m);        /* gs_emit_tile_keys */
 
 /*
  * Pose inverse.  Replaces inverse_SE3_qt_torch (reference utils.py:426-432, used R.py:845).
@@ -92,6 +94,35 @@ int gs_emit_keys(const uint16_t *bbox, const int32_t *depth_key, const int64_t *
 int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *payload_alt,
                   int64_t k, int depth_bits, int tile_bits, void *workspace,
                   int *result_in_alt /*host*/, void *stream);
+
+/*
+ * Depth-first key pipeline (the default product path when depth keys are non-negative, i.e.
+ * near_plane >= 0).  Together the next three calls replace generate_point_sort_key_by_num_overlap_tiles
+ * (R.py:131-172), Tensor.sort() + gather (R.py:947-950) and find_tile_start_and_end (R.py:175-193):
+ * the resulting payload order and tile ranges equal those of a stable sort of the reference's
+ * 64-bit keys (ties in emission order), at a third of the memory traffic.
+ *
+ * gs_sort_points_by_depth: order [m] i32 = row indices of the visible list sorted by depth_key
+ *   (stable; depth_key >= 0 must fit `depth_bits` <= 31 bits).
+ * gs_emit_tile_keys: walks `order`, and for every tile of every point's bounding box writes
+ *   tile_ids [k] u32 and payload [k] i32 (= row index), contiguous per point, points in `order`.
+ * gs_sort_pairs32: stable ascending sort of (u32 key, i32 payload) by the low `key_bits` bits;
+ *   ping-pong buffers and *result_in_alt as gs_sort_pairs.
+ * gs_tile_ranges32: as gs_tile_ranges, on sorted tile ids.
+ * gs_sorted_keys: rebuilds the reference's sorted 64-bit keys (depth_key[payload] + (tile << 32),
+ *   R.py:159-160) for inspection and the parity tests; not on the product path.
+ */
+int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int depth_bits, int32_t *order,
+                            void *workspace, void *stream);
+int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k, int width,
+                      uint32_t *tile_ids, int32_t *payload, void *workspace, void *stream);
+int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_alt, int32_t *payload_alt,
+                    int64_t k, int key_bits, void *workspace, int *result_in_alt /*host*/,
+                    void *stream);
+int gs_tile_ranges32(const uint32_t *sorted_tile_ids, int64_t k, int32_t *tile_start,
+                     int32_t *tile_end, int num_tiles, void *stream);
+int gs_sorted_keys(const uint32_t *sorted_tile_ids, const int32_t *sorted_payload,
+                   const int32_t *depth_key, int64_t k, int64_t *keys, void *stream);
 
 /*
  * Tile ranges.  Replaces find_tile_start_and_end (R.py:175-193).  start/end [num_tiles] i32

@@ -16,6 +16,7 @@ Host-side differences from the reference, none of which change results:
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 from typing import Callable, Dict, Optional
 
@@ -37,6 +38,11 @@ TILE_HEIGHT = 16    # R.py:28
 _lib = _capi.lib
 _REC = 12
 _GRAD_SLOTS = 12
+
+# "depth_first": sort the points by depth, emit tile ids in that order, sort by tile id only (a third
+# of the sort traffic; same payload order and tile ranges).  "literal": build and sort the reference's
+# 64-bit keys (R.py:131-172, 947-950); also taken automatically when depth keys can be negative.
+KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "depth_first")
 
 # set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
 STAGE_PROFILER = None
@@ -237,7 +243,19 @@ class _ForwardState:
     """Everything the backward needs, plus handles a test can read every stage from."""
     __slots__ = ("n", "m", "k", "width", "height", "buffers", "payload", "keys", "tile_start",
                  "tile_end", "image", "depth", "count", "acc_alpha", "last", "q_cam", "t_cam",
-                 "intrinsics", "info", "unsorted_keys", "unsorted_payload")
+                 "intrinsics", "info", "unsorted_keys", "unsorted_payload", "tile_ids")
+
+    def sorted_keys(self) -> torch.Tensor:
+        """The reference's sorted 64-bit keys (point_in_camera_sort_key, R.py:947) of this forward."""
+        if self.keys is not None:
+            return self.keys
+        keys = torch.empty(self.k, dtype=torch.int64, device=self.payload.device)
+        if self.k > 0:
+            stream = torch.cuda.current_stream(keys.device).cuda_stream
+            _capi.check(_lib.gs_sorted_keys(self.tile_ids.data_ptr(), self.payload.data_ptr(),
+                                            self.buffers.ptr("depth_key"), self.k, keys.data_ptr(),
+                                            stream), "gs_sorted_keys")
+        return keys
 
 
 def _check_inputs(pointcloud, features, invalid_mask, object_id, q, t, intrinsics):
@@ -325,32 +343,71 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
 
     depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
                                           float(cfg.depth_to_sort_key_scale), num_tiles)
-    keys2 = torch.empty(2 * max(k, 1), dtype=torch.int64, device=dev)
-    pay2 = torch.empty(2 * max(k, 1), dtype=torch.int32, device=dev)
-    keys_a, keys_b = keys2[:max(k, 1)], keys2[max(k, 1):]
-    pay_a, pay_b = pay2[:max(k, 1)], pay2[max(k, 1):]
-    _mark("host_sync_and_alloc")
-    if k > 0:
-        _capi.check(_lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"), buf.ptr("tile_offsets"),
-                                      m, k, W, keys_a.data_ptr(), pay_a.data_ptr(), stream),
-                    "gs_emit_keys")
-        _mark("emit_keys")
-        if keep_unsorted:
-            st.unsorted_keys, st.unsorted_payload = keys_a[:k].clone(), pay_a[:k].clone()
-        sort_ws = torch.empty(int(_lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
-        in_alt = C.c_int(0)
-        _capi.check(_lib.gs_sort_pairs(keys_a.data_ptr(), pay_a.data_ptr(), keys_b.data_ptr(),
-                                       pay_b.data_ptr(), k, depth_bits, tile_bits,
-                                       sort_ws.data_ptr(), C.byref(in_alt), stream), "gs_sort_pairs")
-        _mark("sort_pairs")
-        st.keys = (keys_b if in_alt.value else keys_a)[:k]
-        st.payload = (pay_b if in_alt.value else pay_a)[:k]
+    depth_first = KEY_PIPELINE == "depth_first" and depth_bits <= 31
+    kk = max(k, 1)
+    st.tile_ids = None
+    if depth_first:
+        # points sorted by depth -> tile ids emitted in that order -> stable sort by tile id only
+        tid2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
+        pay2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
+        order = torch.empty(max(m, 1), dtype=torch.int32, device=dev)
+        ws_bytes = max(int(_lib.gs_point_sort_workspace_bytes(m)), int(_lib.gs_sort_workspace_bytes(k)),
+                       int(_lib.gs_emit_workspace_bytes(m)), 16)
+        sort_ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+        _mark("host_sync_and_alloc")
+        st.keys = None
+        if k > 0:
+            _capi.check(_lib.gs_sort_points_by_depth(buf.ptr("depth_key"), m, depth_bits,
+                                                     order.data_ptr(), sort_ws.data_ptr(), stream),
+                        "gs_sort_points_by_depth")
+            _mark("sort_points")
+            _capi.check(_lib.gs_emit_tile_keys(order.data_ptr(), buf.ptr("bbox"), m, k, W,
+                                               tid2.data_ptr(), pay2.data_ptr(), sort_ws.data_ptr(),
+                                               stream), "gs_emit_tile_keys")
+            _mark("emit_keys")
+            in_alt = C.c_int(0)
+            _capi.check(_lib.gs_sort_pairs32(tid2.data_ptr(), pay2.data_ptr(),
+                                             tid2.data_ptr() + 4 * kk, pay2.data_ptr() + 4 * kk, k,
+                                             tile_bits, sort_ws.data_ptr(), C.byref(in_alt), stream),
+                        "gs_sort_pairs32")
+            _mark("sort_pairs")
+            half = slice(kk, kk + k) if in_alt.value else slice(0, k)
+            st.tile_ids, st.payload = tid2[half], pay2[half]
+        else:
+            st.tile_ids, st.payload = tid2[:0], pay2[:0]
+        _capi.check(_lib.gs_tile_ranges32(st.tile_ids.data_ptr() if k > 0 else None, k,
+                                          st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
+                                          stream), "gs_tile_ranges32")
+        _mark("tile_ranges")
     else:
-        st.keys, st.payload = keys_a[:0], pay_a[:0]
-    _capi.check(_lib.gs_tile_ranges(st.keys.data_ptr() if k > 0 else None, k,
-                                    st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
-                                    stream), "gs_tile_ranges")
-    _mark("tile_ranges")
+        # literal pipeline: the reference's 64-bit keys in emission order, full stable sort
+        keys2 = torch.empty(2 * kk, dtype=torch.int64, device=dev)
+        pay2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
+        keys_a, keys_b = keys2[:kk], keys2[kk:]
+        pay_a, pay_b = pay2[:kk], pay2[kk:]
+        _mark("host_sync_and_alloc")
+        if k > 0:
+            _capi.check(_lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"),
+                                          buf.ptr("tile_offsets"), m, k, W, keys_a.data_ptr(),
+                                          pay_a.data_ptr(), stream), "gs_emit_keys")
+            _mark("emit_keys")
+            if keep_unsorted:
+                st.unsorted_keys, st.unsorted_payload = keys_a[:k].clone(), pay_a[:k].clone()
+            sort_ws = torch.empty(int(_lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
+            in_alt = C.c_int(0)
+            _capi.check(_lib.gs_sort_pairs(keys_a.data_ptr(), pay_a.data_ptr(), keys_b.data_ptr(),
+                                           pay_b.data_ptr(), k, depth_bits, tile_bits,
+                                           sort_ws.data_ptr(), C.byref(in_alt), stream),
+                        "gs_sort_pairs")
+            _mark("sort_pairs")
+            st.keys = (keys_b if in_alt.value else keys_a)[:k]
+            st.payload = (pay_b if in_alt.value else pay_a)[:k]
+        else:
+            st.keys, st.payload = keys_a[:0], pay_a[:0]
+        _capi.check(_lib.gs_tile_ranges(st.keys.data_ptr() if k > 0 else None, k,
+                                        st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
+                                        stream), "gs_tile_ranges")
+        _mark("tile_ranges")
     _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
                                   st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
@@ -358,7 +415,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                 "gs_blend_fwd")
     _mark("blend_fwd")
     st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
-                   tile_bits=tile_bits)
+                   tile_bits=tile_bits, key_pipeline="depth_first" if depth_first else "literal")
     return st
 
 

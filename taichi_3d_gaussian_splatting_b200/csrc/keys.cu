@@ -82,6 +82,141 @@ __global__ void tile_ranges_kernel(const long long *__restrict__ keys, long long
     }
 }
 
+
+// ---- depth-first pipeline -------------------------------------------------------------------------
+// The visible points arrive as `order`: their row indices sorted by depth key (stable).  A block owns
+// 256 consecutive entries of that order, counts their tiles, takes its exclusive offset among all
+// blocks by a decoupled look-back (64-bit status words: flag << 62 | count), and emits its
+// contiguous slot range exactly like emit_keys_kernel -- but the key is the tile id alone.  A
+// stable sort of these pairs by tile id then yields, per tile, depth order with ties in ascending
+// point order: the order a stable sort of the reference's 64-bit keys produces.
+constexpr unsigned long long kEmitAggregate = 1ull << 62;
+constexpr unsigned long long kEmitPrefix = 2ull << 62;
+constexpr unsigned long long kEmitValueMask = (1ull << 62) - 1;
+
+__global__ void __launch_bounds__(kEmitBlock)
+emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ bbox, long long m,
+                      long long k_total, int tiles_per_row, uint32_t *__restrict__ tile_ids,
+                      int32_t *__restrict__ payload, unsigned long long *__restrict__ status,
+                      unsigned int *__restrict__ ticket)
+{
+    __shared__ unsigned int s_end[kEmitBlock];
+    __shared__ ushort4 s_box[kEmitBlock];
+    __shared__ int32_t s_row[kEmitBlock];
+    __shared__ unsigned int s_warp_total[kEmitBlock / 32];
+    __shared__ unsigned long long s_base;
+    __shared__ unsigned int s_ticket;
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) s_ticket = atomicAdd(ticket, 1u);
+    __syncthreads();
+    const int block = (int)s_ticket;
+    const long long first = (long long)block * kEmitBlock;
+    const int npts = (int)min((long long)kEmitBlock, m - first);
+
+    ushort4 box = make_ushort4(0, 0, 0, 0);
+    int row = 0;
+    unsigned int cnt = 0;
+    if (tid < npts) {
+        row = __ldg(order + first + tid);
+        box = bbox[row];
+        cnt = (unsigned int)(((int)box.y - (int)box.x) * ((int)box.w - (int)box.z));
+    }
+    // inclusive scan of the counts over the block
+    unsigned int incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned int o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp_total[warp] = incl;
+    __syncthreads();
+    unsigned int warp_excl = 0, block_total = 0;
+#pragma unroll
+    for (int w = 0; w < kEmitBlock / 32; ++w) {
+        unsigned int t = s_warp_total[w];
+        if (w < warp) warp_excl += t;
+        block_total += t;
+    }
+    s_box[tid] = box;
+    s_row[tid] = row;
+    s_end[tid] = warp_excl + incl;
+    if (warp == 0) {
+        if (lane == 0)
+            gs_st_volatile_u64(status + block, (block == 0 ? kEmitPrefix : kEmitAggregate) | block_total);
+        unsigned long long excl = 0;
+        if (block > 0) {
+            int base = block - 1;
+            while (true) {
+                int idx = base - lane;
+                unsigned long long st = kEmitPrefix;  // positions before block 0: empty prefix
+                if (idx >= 0) {
+                    do { st = gs_ld_volatile_u64(status + idx); } while ((st >> 62) == 0);
+                }
+                unsigned int pmask = __ballot_sync(0xffffffffu, (st >> 62) == 2);
+                int firstp = pmask ? (__ffs(pmask) - 1) : 32;
+                unsigned long long contrib = (lane <= firstp) ? (st & kEmitValueMask) : 0ull;
+#pragma unroll
+                for (int d = 16; d > 0; d >>= 1) contrib += __shfl_xor_sync(0xffffffffu, contrib, d);
+                excl += contrib;
+                if (pmask) break;
+                base -= 32;
+            }
+            if (lane == 0) gs_st_volatile_u64(status + block, kEmitPrefix | (excl + block_total));
+        }
+        if (lane == 0) s_base = excl;
+    }
+    __syncthreads();
+    const unsigned long long base = s_base;
+    const unsigned int total = block_total;
+    for (unsigned int s = tid; s < total; s += kEmitBlock) {
+        int lo = 0, hi = npts - 1;
+        while (lo < hi) {
+            int mid = (lo + hi) >> 1;
+            if (s_end[mid] > s) hi = mid; else lo = mid + 1;
+        }
+        ushort4 b = s_box[lo];
+        int nv = (int)b.w - (int)b.z;
+        int cnt2 = ((int)b.y - (int)b.x) * nv;
+        unsigned int r = s - (s_end[lo] - (unsigned int)cnt2);
+        int tu = (int)b.x + (int)(r / (unsigned int)nv);
+        int tv = (int)b.z + (int)(r % (unsigned int)nv);
+        long long slot = (long long)base + s;
+        if (slot < k_total) {
+            tile_ids[slot] = (uint32_t)(tu + tv * tiles_per_row);
+            payload[slot] = s_row[lo];
+        }
+    }
+}
+
+__global__ void tile_ranges32_kernel(const uint32_t *__restrict__ tile_ids, long long k,
+                                     int32_t *__restrict__ tile_start, int32_t *__restrict__ tile_end,
+                                     int num_tiles)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    unsigned t = tile_ids[i];
+    if (i + 1 < k) {
+        unsigned tn = tile_ids[i + 1];
+        if (t != tn) {
+            if (tn < (unsigned)num_tiles) tile_start[tn] = (int32_t)(i + 1);
+            if (t < (unsigned)num_tiles) tile_end[t] = (int32_t)(i + 1);
+        }
+    } else if (t < (unsigned)num_tiles) {
+        tile_end[t] = (int32_t)k;
+    }
+}
+
+// the reference's 64-bit key of every sorted entry, rebuilt for inspection (R.py:159-160)
+__global__ void sorted_keys_kernel(const uint32_t *__restrict__ tile_ids, const int32_t *__restrict__ payload,
+                                   const int32_t *__restrict__ depth_key, long long k,
+                                   long long *__restrict__ keys)
+{
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= k) return;
+    keys[i] = (long long)depth_key[payload[i]] + ((long long)tile_ids[i] << 32);
+}
+
 }  // namespace
 
 extern "C" int gs_emit_keys(const uint16_t *bbox, const int32_t *depth_key,
@@ -114,6 +249,63 @@ extern "C" int gs_tile_ranges(const int64_t *sorted_keys, int64_t k, int32_t *ti
     long long blocks = (k + threads - 1) / threads;
     tile_ranges_kernel<<<(unsigned)blocks, threads, 0, st>>>((const long long *)sorted_keys, k,
                                                              tile_start, tile_end, num_tiles);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+extern "C" int64_t gs_emit_workspace_bytes(int64_t m)
+{
+    int64_t blocks = (m + kEmitBlock - 1) / kEmitBlock;
+    return (blocks + 2) * 8;
+}
+
+extern "C" int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k,
+                                 int width, uint32_t *tile_ids, int32_t *payload, void *workspace,
+                                 void *stream)
+{
+    if (m < 0 || k < 0 || width <= 0 || width % kTile) return GS_E_INVALID;
+    if (k >= (1ll << 31)) return GS_E_CAPACITY;  // int32 indices downstream (R.py:930, 954-957)
+    if (m == 0 || k == 0) return GS_OK;
+    if (!order || !bbox || !tile_ids || !payload || !workspace) return GS_E_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    int blocks = (int)((m + kEmitBlock - 1) / kEmitBlock);
+    GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, (size_t)gs_emit_workspace_bytes(m), st));
+    unsigned long long *status = (unsigned long long *)workspace;
+    emit_tile_keys_kernel<<<blocks, kEmitBlock, 0, st>>>(
+        order, reinterpret_cast<const ushort4 *>(bbox), m, k, width / kTile, tile_ids, payload, status,
+        (unsigned int *)(status + blocks));
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+extern "C" int gs_tile_ranges32(const uint32_t *sorted_tile_ids, int64_t k, int32_t *tile_start,
+                                int32_t *tile_end, int num_tiles, void *stream)
+{
+    if (k < 0 || num_tiles <= 0 || !tile_start || !tile_end) return GS_E_INVALID;
+    if (k >= (1ll << 31)) return GS_E_CAPACITY;
+    cudaStream_t st = (cudaStream_t)stream;
+    GS_CUDA_TRY(cudaMemsetAsync(tile_start, 0, sizeof(int32_t) * (size_t)num_tiles, st));
+    GS_CUDA_TRY(cudaMemsetAsync(tile_end, 0, sizeof(int32_t) * (size_t)num_tiles, st));
+    if (k == 0) return GS_OK;
+    if (!sorted_tile_ids) return GS_E_INVALID;
+    int threads = 256;
+    long long blocks = (k + threads - 1) / threads;
+    tile_ranges32_kernel<<<(unsigned)blocks, threads, 0, st>>>(sorted_tile_ids, k, tile_start, tile_end,
+                                                               num_tiles);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+extern "C" int gs_sorted_keys(const uint32_t *sorted_tile_ids, const int32_t *sorted_payload,
+                              const int32_t *depth_key, int64_t k, int64_t *keys, void *stream)
+{
+    if (k < 0) return GS_E_INVALID;
+    if (k == 0) return GS_OK;
+    if (!sorted_tile_ids || !sorted_payload || !depth_key || !keys) return GS_E_INVALID;
+    int threads = 256;
+    long long blocks = (k + threads - 1) / threads;
+    sorted_keys_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(
+        sorted_tile_ids, sorted_payload, depth_key, k, (long long *)keys);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

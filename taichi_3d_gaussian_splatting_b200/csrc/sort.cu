@@ -1,14 +1,18 @@
-// sort.cu -- stable LSD radix sort of (int64 key, int32 payload) pairs, onesweep style:
-// one histogram pass over the keys, then one read + one scattered write per 8-bit digit with
-// a decoupled look-back over the per-tile digit counts (no separate scan pass).
+// sort.cu -- stable LSD radix sorts, onesweep style: one histogram pass over the keys, then one
+// read + one scattered write per 8-bit digit with a decoupled look-back over the per-tile digit
+// counts (no separate scan pass).  Ties keep their input order.
 //
-// Replaces Tensor.sort() + gather (reference R.py:947-950).  Ties keep their input order
-// (emission-slot order), which fixes the order torch leaves unspecified.
-//
-// Only the significant bits are sorted.  A key is depth + (tile << 32); the host passes how many
-// low bits the depth needs and how many bits the tile id needs, and the digits are taken from the
-// compacted value (tile << depth_bits) | depth.  depth_bits = tile_bits = 32 selects a full
-// signed 64-bit sort (sign bit flipped), used when depths may be negative.
+// Two users:
+//   * the depth-first pipeline (default): the M visible points are sorted by their 32-bit depth
+//     key (gs_sort_points_by_depth, values = row indices generated on the fly), tile keys are
+//     emitted in that order, and the K (tile id, payload) pairs are sorted by tile id only
+//     (gs_sort_pairs32) -- 8 bytes per pair and two passes at C2 instead of 12 bytes and four;
+//   * the literal pipeline: (int64 key, int32 payload) pairs as the reference builds them
+//     (gs_sort_pairs; replaces Tensor.sort() + gather, reference R.py:947-950).  Only the
+//     significant bits are sorted: a key is depth + (tile << 32); the host passes how many low
+//     bits the depth needs and how many bits the tile id needs, and the digits are taken from
+//     the compacted value (tile << depth_bits) | depth.  depth_bits = tile_bits = 32 selects a
+//     full signed 64-bit sort (sign bit flipped), used when depths may be negative.
 #include "gs_common.cuh"
 
 namespace {
@@ -36,9 +40,12 @@ __device__ __forceinline__ unsigned long long compact_key(long long key, const K
     unsigned long long c = (s.depth_bits >= 32) ? u : ((hi << s.depth_bits) | (lo & s.depth_mask));
     return c ^ s.xor_mask;
 }
+// 32-bit keys are sorted as they are (the spec is ignored)
+__device__ __forceinline__ unsigned int compact_key(unsigned int key, const KeySpec &) { return key; }
 
+template <typename KeyT>
 __global__ void __launch_bounds__(256)
-histogram_kernel(const long long *__restrict__ keys, long long k, KeySpec spec, int num_passes,
+histogram_kernel(const KeyT *__restrict__ keys, long long k, KeySpec spec, int num_passes,
                  uint32_t *__restrict__ ghist)
 {
     __shared__ uint32_t sh[kMaxPasses * kRadix];
@@ -46,7 +53,7 @@ histogram_kernel(const long long *__restrict__ keys, long long k, KeySpec spec, 
     __syncthreads();
     long long stride = (long long)gridDim.x * blockDim.x;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < k; i += stride) {
-        unsigned long long c = compact_key(keys[i], spec);
+        auto c = compact_key(keys[i], spec);
         for (int p = 0; p < num_passes; ++p)
             atomicAdd(&sh[p * kRadix + (int)((c >> (8 * p)) & 0xff)], 1u);
     }
@@ -75,14 +82,16 @@ scan_histogram_kernel(const uint32_t *__restrict__ ghist, uint32_t *__restrict__
     gbase[blockIdx.x * kRadix + tid] = off + incl - v;
 }
 
+// vals_in == nullptr: the value of an element is its index (first pass of an argsort)
+template <typename KeyT>
 __global__ void __launch_bounds__(kSortBlock)
-onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
-                long long *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
+onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
+                KeyT *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
                 KeySpec spec, int shift, const uint32_t *__restrict__ gbase,
                 uint32_t *__restrict__ status, unsigned int *__restrict__ ticket)
 {
     extern __shared__ __align__(16) unsigned char smem[];
-    long long *s_keys = reinterpret_cast<long long *>(smem);
+    KeyT *s_keys = reinterpret_cast<KeyT *>(smem);
     int32_t *s_vals = reinterpret_cast<int32_t *>(s_keys + kSortTile);
     uint32_t *s_warp_hist = reinterpret_cast<uint32_t *>(s_vals + kSortTile);
     uint32_t *s_digit_base = s_warp_hist + kSortWarps * kRadix;
@@ -99,7 +108,7 @@ onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict
     const long long tile_base = tile * kSortTile;
     const int valid = (int)min((long long)kSortTile, k - tile_base);
 
-    long long key[kItems];
+    KeyT key[kItems];
     int32_t val[kItems];
     const int warp_first = warp * (kItems * 32);
 #pragma unroll
@@ -107,7 +116,7 @@ onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict
         int local = warp_first + j * 32 + lane;
         if (local < valid) {
             key[j] = keys_in[tile_base + local];
-            val[j] = vals_in[tile_base + local];
+            val[j] = vals_in ? vals_in[tile_base + local] : (int32_t)(tile_base + local);
         } else {
             key[j] = 0;
             val[j] = 0;
@@ -194,7 +203,7 @@ onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict
 
     // ---- coalesced write-out: consecutive smem slots of one digit are consecutive in global -----
     for (int i = tid; i < valid; i += kSortBlock) {
-        long long kk = s_keys[i];
+        KeyT kk = s_keys[i];
         int d = (int)((compact_key(kk, spec) >> shift) & 0xff);
         uint32_t pos = (uint32_t)i + s_global_off[d];
         keys_out[pos] = kk;
@@ -202,17 +211,76 @@ onesweep_kernel(const long long *__restrict__ keys_in, const int32_t *__restrict
     }
 }
 
-constexpr size_t kSortSmem = (size_t)kSortTile * 12 + (size_t)kSortWarps * kRadix * 4 +
-                             (size_t)kRadix * 8 + (size_t)kSortWarps * 4;
+constexpr size_t sort_smem(size_t key_bytes)
+{
+    return (size_t)kSortTile * (key_bytes + 4) + (size_t)kSortWarps * kRadix * 4 +
+           (size_t)kRadix * 8 + (size_t)kSortWarps * 4;
+}
 
 inline int64_t sort_tiles(int64_t k) { return (k + kSortTile - 1) / kSortTile; }
 
+// Runs `num_passes` onesweep passes over k elements.  The first pass reads (keys_first,
+// vals_first) -- vals_first may be null (values = indices) -- and writes (keys_a, vals_a); later
+// passes ping-pong between the a and b buffers.  Workspace layout:
+// ghist | gbase | tickets (64 B) | status[passes][tiles][256].
+template <typename KeyT>
+int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, int32_t *vals_a,
+              KeyT *keys_b, int32_t *vals_b, int64_t k, const KeySpec &spec, int num_passes,
+              void *workspace, cudaStream_t st)
+{
+    const int64_t tiles = sort_tiles(k);
+    uint32_t *ghist = (uint32_t *)workspace;
+    uint32_t *gbase = ghist + kMaxPasses * kRadix;
+    unsigned int *tickets = (unsigned int *)(gbase + kMaxPasses * kRadix);
+    uint32_t *status = (uint32_t *)(tickets + 16);
+    size_t used = (size_t)kMaxPasses * kRadix * 4 * 2 + 64 + (size_t)num_passes * tiles * kRadix * 4;
+    GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, used, st));
+
+    static bool attr_set = false;  // one flag per KeyT instantiation
+    if (!attr_set) {
+        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel<KeyT>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sort_smem(sizeof(KeyT))));
+        attr_set = true;
+    }
+
+    int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
+    if (hist_blocks < 1) hist_blocks = 1;
+    histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, spec, num_passes, ghist);
+    GS_LAUNCH_CHECK();
+    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ghist, gbase);
+    GS_LAUNCH_CHECK();
+
+    const KeyT *kin = keys_first;
+    const int32_t *vin = vals_first;
+    for (int p = 0; p < num_passes; ++p) {
+        KeyT *kout = (p & 1) ? keys_b : keys_a;
+        int32_t *vout = (p & 1) ? vals_b : vals_a;
+        onesweep_kernel<KeyT><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
+            kin, vin, kout, vout, k, spec, 8 * p, gbase + p * kRadix,
+            status + (size_t)p * tiles * kRadix, tickets + p);
+        GS_LAUNCH_CHECK();
+        kin = kout;
+        vin = vout;
+    }
+    return GS_OK;
+}
+
+inline int64_t sort_scratch_bytes(int64_t k)
+{
+    return (int64_t)kMaxPasses * kRadix * 4 * 2 + 64 + (int64_t)kMaxPasses * sort_tiles(k) * kRadix * 4;
+}
+
+inline int64_t align256(int64_t x) { return (x + 255) / 256 * 256; }
+
 }  // namespace
 
-extern "C" int64_t gs_sort_workspace_bytes(int64_t k)
+extern "C" int64_t gs_sort_workspace_bytes(int64_t k) { return sort_scratch_bytes(k); }
+
+extern "C" int64_t gs_point_sort_workspace_bytes(int64_t m)
 {
-    // ghist | gbase | tickets (64 B) | status[passes][tiles][256]
-    return (int64_t)kMaxPasses * kRadix * 4 * 2 + 64 + (int64_t)kMaxPasses * sort_tiles(k) * kRadix * 4;
+    // scratch | keys a | keys b | values tmp
+    return align256(sort_scratch_bytes(m)) + 3 * align256(4 * (m > 0 ? m : 1));
 }
 
 extern "C" int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt,
@@ -225,49 +293,58 @@ extern "C" int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt,
     if (k >= (1ll << 30)) return GS_E_CAPACITY;  // 30-bit counts in the look-back words
     if (k <= 1) return GS_OK;
     if (!keys || !payload || !keys_alt || !payload_alt || !workspace) return GS_E_INVALID;
-    cudaStream_t st = (cudaStream_t)stream;
 
     KeySpec spec;
     spec.depth_bits = depth_bits;
     spec.depth_mask = depth_bits >= 32 ? 0xffffffffull : ((1ull << depth_bits) - 1ull);
     const bool full = (depth_bits == 32 && tile_bits == 32);
     spec.xor_mask = full ? 0x8000000000000000ull : 0ull;
-    int total_bits = depth_bits + tile_bits;
-    int num_passes = (total_bits + 7) / 8;
+    int num_passes = (depth_bits + tile_bits + 7) / 8;
     if (num_passes == 0) return GS_OK;
-
-    const int64_t tiles = sort_tiles(k);
-    uint32_t *ghist = (uint32_t *)workspace;
-    uint32_t *gbase = ghist + kMaxPasses * kRadix;
-    unsigned int *tickets = (unsigned int *)(gbase + kMaxPasses * kRadix);
-    uint32_t *status = (uint32_t *)(tickets + 16);
-    size_t used = (size_t)kMaxPasses * kRadix * 4 * 2 + 64 + (size_t)num_passes * tiles * kRadix * 4;
-    GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, used, st));
-
-    static bool attr_set = false;
-    if (!attr_set) {
-        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                         (int)kSortSmem));
-        attr_set = true;
-    }
-
-    int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
-    if (hist_blocks < 1) hist_blocks = 1;
-    histogram_kernel<<<hist_blocks, 256, 0, st>>>((const long long *)keys, k, spec, num_passes, ghist);
-    GS_LAUNCH_CHECK();
-    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ghist, gbase);
-    GS_LAUNCH_CHECK();
-
-    long long *kin = (long long *)keys, *kout = (long long *)keys_alt;
-    int32_t *vin = payload, *vout = payload_alt;
-    for (int p = 0; p < num_passes; ++p) {
-        onesweep_kernel<<<(unsigned)tiles, kSortBlock, kSortSmem, st>>>(
-            kin, vin, kout, vout, k, spec, 8 * p, gbase + p * kRadix,
-            status + (size_t)p * tiles * kRadix, tickets + p);
-        GS_LAUNCH_CHECK();
-        long long *tk = kin; kin = kout; kout = tk;
-        int32_t *tv = vin; vin = vout; vout = tv;
-    }
+    // pass 0 writes the alt buffers, pass 1 the primary ones, ...
+    int rc = sort_impl<long long>((const long long *)keys, payload, (long long *)keys_alt, payload_alt,
+                                  (long long *)keys, payload, k, spec, num_passes, workspace,
+                                  (cudaStream_t)stream);
+    if (rc != GS_OK) return rc;
     if (result_in_alt) *result_in_alt = (num_passes & 1);
     return GS_OK;
+}
+
+extern "C" int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_alt,
+                               int32_t *payload_alt, int64_t k, int key_bits, void *workspace,
+                               int *result_in_alt, void *stream)
+{
+    if (result_in_alt) *result_in_alt = 0;
+    if (k < 0 || key_bits < 0 || key_bits > 32) return GS_E_INVALID;
+    if (k >= (1ll << 30)) return GS_E_CAPACITY;
+    if (k <= 1 || key_bits == 0) return GS_OK;
+    if (!keys || !payload || !keys_alt || !payload_alt || !workspace) return GS_E_INVALID;
+    KeySpec spec = {32, 0xffffffffull, 0ull};
+    int num_passes = (key_bits + 7) / 8;
+    int rc = sort_impl<unsigned int>(keys, payload, keys_alt, payload_alt, keys, payload, k, spec,
+                                     num_passes, workspace, (cudaStream_t)stream);
+    if (rc != GS_OK) return rc;
+    if (result_in_alt) *result_in_alt = (num_passes & 1);
+    return GS_OK;
+}
+
+extern "C" int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int depth_bits,
+                                       int32_t *order, void *workspace, void *stream)
+{
+    if (m < 0 || depth_bits < 1 || depth_bits > 31) return GS_E_INVALID;
+    if (m >= (1ll << 30)) return GS_E_CAPACITY;
+    if (m == 0) return GS_OK;
+    if (!depth_key || !order || !workspace) return GS_E_INVALID;
+    unsigned char *ws = (unsigned char *)workspace;
+    const int64_t scratch = align256(sort_scratch_bytes(m)), col = align256(4 * m);
+    unsigned int *keys_a = (unsigned int *)(ws + scratch);
+    unsigned int *keys_b = (unsigned int *)(ws + scratch + col);
+    int32_t *vals_tmp = (int32_t *)(ws + scratch + 2 * col);
+    KeySpec spec = {32, 0xffffffffull, 0ull};
+    const int num_passes = (depth_bits + 7) / 8;
+    // the last pass must land in `order`: pass p writes the a buffers when p is even
+    int32_t *vals_a = (num_passes & 1) ? order : vals_tmp;
+    int32_t *vals_b = (num_passes & 1) ? vals_tmp : order;
+    return sort_impl<unsigned int>((const unsigned int *)depth_key, nullptr, keys_a, vals_a, keys_b,
+                                   vals_b, m, spec, num_passes, workspace, (cudaStream_t)stream);
 }

@@ -62,6 +62,93 @@ def test_sort_full_signed_64bit(k):
     assert np.array_equal(sv, order.astype(np.int32))
 
 
+@pytest.mark.parametrize("k", [1, 2, 33, 4096, 4097, 250001, 3000000])
+@pytest.mark.parametrize("bits", [13, 8, 16, 3, 17])
+def test_sort_pairs32_stable(k, bits):
+    """(u32 tile id, i32 payload) pairs by the low `bits` bits, ties in input order."""
+    capi = _lib()
+    rng = np.random.default_rng(k * 7 + bits)
+    keys_np = rng.integers(0, min(1 << bits, 9000), k, dtype=np.int64).astype(np.uint32)
+    dev = torch.device("cuda")
+    keys = torch.from_numpy(keys_np.view(np.int32).copy()).to(dev)
+    vals = torch.arange(k, dtype=torch.int32, device=dev)
+    keys_alt, vals_alt = torch.empty_like(keys), torch.empty_like(vals)
+    ws = torch.empty(int(capi.lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
+    in_alt = C.c_int(0)
+    capi.check(capi.lib.gs_sort_pairs32(keys.data_ptr(), vals.data_ptr(), keys_alt.data_ptr(),
+                                        vals_alt.data_ptr(), k, bits, ws.data_ptr(), C.byref(in_alt),
+                                        torch.cuda.current_stream().cuda_stream), "gs_sort_pairs32")
+    torch.cuda.synchronize()
+    rk, rv = (keys_alt, vals_alt) if in_alt.value else (keys, vals)
+    order = np.argsort(keys_np, kind="stable")
+    assert np.array_equal(rk.cpu().numpy().view(np.uint32), keys_np[order])
+    assert np.array_equal(rv.cpu().numpy(), order.astype(np.int32))
+
+
+@pytest.mark.parametrize("m", [1, 31, 4097, 70001, 1000000])
+@pytest.mark.parametrize("bits", [17, 8, 24, 31, 1])
+def test_sort_points_by_depth_is_a_stable_argsort(m, bits):
+    capi = _lib()
+    rng = np.random.default_rng(m + bits)
+    depth = rng.integers(0, min(1 << bits, 5000) if bits < 24 else (1 << bits), m, dtype=np.int64)
+    depth = depth.astype(np.int32)
+    dev = torch.device("cuda")
+    d = torch.from_numpy(depth).to(dev)
+    order = torch.empty(m, dtype=torch.int32, device=dev)
+    ws = torch.empty(int(capi.lib.gs_point_sort_workspace_bytes(m)), dtype=torch.uint8, device=dev)
+    capi.check(capi.lib.gs_sort_points_by_depth(d.data_ptr(), m, bits, order.data_ptr(), ws.data_ptr(),
+                                                torch.cuda.current_stream().cuda_stream),
+               "gs_sort_points_by_depth")
+    torch.cuda.synchronize()
+    assert np.array_equal(d.cpu().numpy(), depth)  # input untouched
+    assert np.array_equal(order.cpu().numpy(), np.argsort(depth, kind="stable").astype(np.int32))
+
+
+def test_emit_tile_keys_follows_the_given_order():
+    """Tile ids / payload contiguous per point, points in `order`; whole-image, single-tile and
+    zero-tile boxes mixed; tile ranges from the sorted ids."""
+    capi = _lib()
+    W, H = 320, 208
+    tw, th = W // 16, H // 16
+    rng = np.random.default_rng(9)
+    m = 3000
+    tu0 = rng.integers(0, tw + 1, m); tu1 = np.minimum(tu0 + rng.integers(0, 6, m), tw)
+    tv0 = rng.integers(0, th + 1, m); tv1 = np.minimum(tv0 + rng.integers(0, 6, m), th)
+    tu0[::13], tu1[::13], tv0[::13], tv1[::13] = 0, tw, 0, th
+    bbox = np.stack([tu0, tu1, tv0, tv1], 1).astype(np.uint16)
+    order_np = rng.permutation(m).astype(np.int32)
+    ids_ref, pay_ref = [], []
+    for r in order_np:
+        for u in range(bbox[r, 0], bbox[r, 1]):
+            for v in range(bbox[r, 2], bbox[r, 3]):
+                ids_ref.append(u + v * tw)
+                pay_ref.append(r)
+    k = len(ids_ref)
+    dev = torch.device("cuda")
+    d_bbox = torch.from_numpy(bbox.view(np.int16)).to(dev)
+    d_order = torch.from_numpy(order_np).to(dev)
+    ids = torch.empty(k, dtype=torch.int32, device=dev)
+    pay = torch.empty(k, dtype=torch.int32, device=dev)
+    ws = torch.empty(int(capi.lib.gs_emit_workspace_bytes(m)), dtype=torch.uint8, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    capi.check(capi.lib.gs_emit_tile_keys(d_order.data_ptr(), d_bbox.data_ptr(), m, k, W, ids.data_ptr(),
+                                          pay.data_ptr(), ws.data_ptr(), st), "gs_emit_tile_keys")
+    torch.cuda.synchronize()
+    assert np.array_equal(ids.cpu().numpy(), np.asarray(ids_ref, np.int32))
+    assert np.array_equal(pay.cpu().numpy(), np.asarray(pay_ref, np.int32))
+    sorted_ids = torch.sort(ids.to(torch.int64)).values.to(torch.int32)
+    start = torch.empty(tw * th, dtype=torch.int32, device=dev)
+    end = torch.empty(tw * th, dtype=torch.int32, device=dev)
+    capi.check(capi.lib.gs_tile_ranges32(sorted_ids.data_ptr(), k, start.data_ptr(), end.data_ptr(),
+                                         tw * th, st), "gs_tile_ranges32")
+    torch.cuda.synchronize()
+    counts = np.bincount(np.asarray(ids_ref), minlength=tw * th)
+    s_np, e_np = start.cpu().numpy(), end.cpu().numpy()
+    assert np.array_equal(e_np - s_np, counts)
+    nz = counts > 0
+    assert np.array_equal(s_np[nz], (np.cumsum(counts) - counts)[nz]) and not s_np[~nz].any()
+
+
 def test_tile_ranges_reference_golden_vector():
     """tests/GaussianPointCloudRasterisation_test.py:18-51 of the reference, same call."""
     from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import find_tile_start_and_end

@@ -28,13 +28,21 @@ SCENES = {
 }
 
 
-@pytest.fixture(scope="module", params=list(SCENES))
+# both key pipelines must give the reference's sorted keys, payload order and tile ranges
+CASES = [(name, "depth_first") for name in SCENES] + \
+        [(name, "literal") for name in ("c1_1k_64x64", "dense_deep_lists_32x32", "truck_cfg_100k_976x544")]
+
+
+@pytest.fixture(scope="module", params=CASES, ids=lambda c: f"{c[0]}-{c[1]}")
 def case(request, oracle32):
-    kwargs, (near, far, scale) = SCENES[request.param]
+    name, pipeline = request.param
+    kwargs, (near, far, scale) = SCENES[name]
     scene = make_scene(**kwargs)
     ref = util.oracle_forward(oracle32, scene, near, far, scale)
-    got = util.cuda_forward_stages(scene, near, far, scale)
-    return dict(name=request.param, scene=scene, ref=ref, got=got, cfg=(near, far, scale))
+    got = util.cuda_forward_stages(scene, near, far, scale, pipeline=pipeline)
+    assert got["_state"].info["key_pipeline"] == pipeline
+    return dict(name=f"{name}-{pipeline}", scene=scene, ref=ref, got=got, cfg=(near, far, scale),
+                pipeline=pipeline)
 
 
 def test_forward_every_stage_exact(case):
@@ -143,7 +151,7 @@ def test_backward_gradients(case, oracle32, oracle64, band):
 
 def test_forward_is_deterministic(case):
     near, far, scale = case["cfg"]
-    again = util.cuda_forward_stages(case["scene"], near, far, scale)
+    again = util.cuda_forward_stages(case["scene"], near, far, scale, pipeline=case["pipeline"])
     assert not util.mismatch_report(case["got"], again)
 
 

@@ -29,8 +29,25 @@ def oracle_forward(oracle, scene, near=0.8, far=1000.0, scale=100.0, rgb_only=Fa
                           scene.height, near, far, scale, rgb_only)
 
 
-def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False):
-    """Run the product forward through its C ABI and return every stage as numpy arrays."""
+def literal_unsorted_keys(st, width):
+    """The reference's unsorted keys / payload in emission order (R.py:131-172), from the literal
+    emission entry point run on the forward's per-point buffers."""
+    from taichi_3d_gaussian_splatting_b200 import _capi
+    dev = st.payload.device
+    keys = torch.empty(max(st.k, 1), dtype=torch.int64, device=dev)
+    pay = torch.empty(max(st.k, 1), dtype=torch.int32, device=dev)
+    if st.k > 0:
+        buf = st.buffers
+        _capi.check(_capi.lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"),
+                                           buf.ptr("tile_offsets"), st.m, st.k, width,
+                                           keys.data_ptr(), pay.data_ptr(),
+                                           torch.cuda.current_stream(dev).cuda_stream), "gs_emit_keys")
+    return keys[:st.k], pay[:st.k]
+
+
+def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False, pipeline=None):
+    """Run the product forward through its C ABI and return every stage as numpy arrays.
+    pipeline: None (the module default), "depth_first" or "literal"."""
     from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
     import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
     from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
@@ -40,10 +57,18 @@ def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False
         near_plane=near, far_plane=far, depth_to_sort_key_scale=scale, rgb_only=rgb_only)
     cam = CameraInfo(camera_intrinsics=t["camera_intrinsics"], camera_height=scene.height,
                      camera_width=scene.width, camera_id=0)
-    st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"],
-                            t["point_invalid_mask"], t["point_object_id"],
-                            t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
-                            keep_unsorted=True)
+    saved = impl.KEY_PIPELINE
+    if pipeline is not None:
+        impl.KEY_PIPELINE = pipeline
+    try:
+        st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"],
+                                t["point_invalid_mask"], t["point_object_id"],
+                                t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
+                                keep_unsorted=True)
+    finally:
+        impl.KEY_PIPELINE = saved
+    if st.unsorted_keys is None and st.k > 0:
+        st.unsorted_keys, st.unsorted_payload = literal_unsorted_keys(st, scene.width)
     torch.cuda.synchronize()
     m, k, buf = st.m, st.k, st.buffers
     np_ = lambda x: x.detach().cpu().numpy()
@@ -58,7 +83,7 @@ def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False
         num_overlap_tiles=np_(buf.view("num_tiles", m)),
         accumulated_num_overlap_tiles=np_(buf.view("tile_offsets", m)),
         records=np_(buf.view("records", m)),
-        point_in_camera_sort_key=np_(st.keys),
+        point_in_camera_sort_key=np_(st.sorted_keys()),
         point_offset_with_sort_key=np_(st.payload),
         tile_points_start=np_(st.tile_start),
         tile_points_end=np_(st.tile_end),
