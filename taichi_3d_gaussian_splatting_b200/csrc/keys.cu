@@ -189,21 +189,38 @@ emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restri
     }
 }
 
-__global__ void tile_ranges32_kernel(const uint32_t *__restrict__ tile_ids, long long k,
-                                     int32_t *__restrict__ tile_start, int32_t *__restrict__ tile_end,
-                                     int num_tiles)
+// four ids per thread (one 16-byte load when the array is 16-byte aligned) plus the successor
+__global__ void __launch_bounds__(256)
+tile_ranges32_kernel(const uint32_t *__restrict__ tile_ids, long long k, int32_t *__restrict__ tile_start,
+                     int32_t *__restrict__ tile_end, int num_tiles, int aligned)
 {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= k) return;
-    unsigned t = tile_ids[i];
-    if (i + 1 < k) {
-        unsigned tn = tile_ids[i + 1];
-        if (t != tn) {
-            if (tn < (unsigned)num_tiles) tile_start[tn] = (int32_t)(i + 1);
-            if (t < (unsigned)num_tiles) tile_end[t] = (int32_t)(i + 1);
+    const long long i0 = 4 * ((long long)blockIdx.x * blockDim.x + threadIdx.x);
+    if (i0 >= k) return;
+    unsigned t[5];
+    const int n = (int)min(4ll, k - i0);
+    if (aligned && n == 4) {
+        const uint4 q = __ldg(reinterpret_cast<const uint4 *>(tile_ids + i0));
+        t[0] = q.x; t[1] = q.y; t[2] = q.z; t[3] = q.w;
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) t[j] = (j < n) ? __ldg(tile_ids + i0 + j) : 0u;
+    }
+    const bool has_next = i0 + n < k;
+    t[4] = has_next ? __ldg(tile_ids + i0 + n) : 0u;
+    if (n < 4) t[n] = t[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        if (j >= n) break;
+        const long long i = i0 + j;
+        if (j + 1 < n || has_next) {
+            const unsigned a = t[j], b = t[j + 1];
+            if (a != b) {
+                if (b < (unsigned)num_tiles) tile_start[b] = (int32_t)(i + 1);
+                if (a < (unsigned)num_tiles) tile_end[a] = (int32_t)(i + 1);
+            }
+        } else if (t[j] < (unsigned)num_tiles) {
+            tile_end[t[j]] = (int32_t)k;
         }
-    } else if (t < (unsigned)num_tiles) {
-        tile_end[t] = (int32_t)k;
     }
 }
 
@@ -289,9 +306,10 @@ extern "C" int gs_tile_ranges32(const uint32_t *sorted_tile_ids, int64_t k, int3
     if (k == 0) return GS_OK;
     if (!sorted_tile_ids) return GS_E_INVALID;
     int threads = 256;
-    long long blocks = (k + threads - 1) / threads;
+    long long blocks = ((k + 3) / 4 + threads - 1) / threads;
+    int aligned = ((uintptr_t)sorted_tile_ids % 16) == 0;
     tile_ranges32_kernel<<<(unsigned)blocks, threads, 0, st>>>(sorted_tile_ids, k, tile_start, tile_end,
-                                                               num_tiles);
+                                                               num_tiles, aligned);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

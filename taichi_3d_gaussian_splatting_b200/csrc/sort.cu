@@ -13,6 +13,8 @@
 //     bits the depth needs and how many bits the tile id needs, and the digits are taken from
 //     the compacted value (tile << depth_bits) | depth.  depth_bits = tile_bits = 32 selects a
 //     full signed 64-bit sort (sign bit flipped), used when depths may be negative.
+#include <cstdlib>
+
 #include "gs_common.cuh"
 
 namespace {
@@ -83,11 +85,14 @@ scan_histogram_kernel(const uint32_t *__restrict__ ghist, uint32_t *__restrict__
 }
 
 // vals_in == nullptr: the value of an element is its index (first pass of an argsort)
-template <typename KeyT>
-__global__ void __launch_bounds__(kSortBlock)
+// digit_bits (1..8): how many bits of this pass's digit can be non-zero (the last pass of a key
+// whose width is not a multiple of 8 has fewer).  kBallot: build the peer masks from digit_bits
+// warp ballots instead of match.any.
+template <typename KeyT, bool kBallot>
+__global__ void __launch_bounds__(kSortBlock, sizeof(KeyT) == 4 ? 3 : 2)
 onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
                 KeyT *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
-                KeySpec spec, int shift, const uint32_t *__restrict__ gbase,
+                KeySpec spec, int shift, int digit_bits, const uint32_t *__restrict__ gbase,
                 uint32_t *__restrict__ status, unsigned int *__restrict__ ticket)
 {
     extern __shared__ __align__(16) unsigned char smem[];
@@ -111,36 +116,72 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
     KeyT key[kItems];
     int32_t val[kItems];
     const int warp_first = warp * (kItems * 32);
+    if (valid == kSortTile) {  // every tile but the last: no per-item bounds checks
+        const KeyT *kp = keys_in + tile_base + warp_first + lane;
 #pragma unroll
-    for (int j = 0; j < kItems; ++j) {
-        int local = warp_first + j * 32 + lane;
-        if (local < valid) {
-            key[j] = keys_in[tile_base + local];
-            val[j] = vals_in ? vals_in[tile_base + local] : (int32_t)(tile_base + local);
+        for (int j = 0; j < kItems; ++j) key[j] = kp[j * 32];
+        if (vals_in) {
+            const int32_t *vp = vals_in + tile_base + warp_first + lane;
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) val[j] = vp[j * 32];
         } else {
-            key[j] = 0;
-            val[j] = 0;
+#pragma unroll
+            for (int j = 0; j < kItems; ++j) val[j] = (int32_t)(tile_base + warp_first + j * 32 + lane);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            int local = warp_first + j * 32 + lane;
+            if (local < valid) {
+                key[j] = keys_in[tile_base + local];
+                val[j] = vals_in ? vals_in[tile_base + local] : (int32_t)(tile_base + local);
+            } else {
+                key[j] = 0;
+                val[j] = 0;
+            }
         }
     }
 
     // ---- warp-level stable ranking per digit (match.any) ---------------------------------
+    // Three unrolled phases so that the 16 items' match -> shared atomic -> shuffle chains
+    // overlap instead of running back to back: (1) peer masks, (2) the lowest peer adds the group
+    // size to the warp's digit counter and keeps the old value (shared atomics of one warp to
+    // one address retire in issue order, so item j is ranked before item j+1), (3) broadcast.
     uint32_t rank[kItems];
+    unsigned int peers[kItems];
     const unsigned int lanemask_lt = (1u << lane) - 1u;
     uint32_t *my_hist = s_warp_hist + warp * kRadix;
+    const int pad_digit = (1 << digit_bits) - 1;  // padding of the last tile: the largest digit
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
         int local = warp_first + j * 32 + lane;
-        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : 255;
-        unsigned int peers = __match_any_sync(0xffffffffu, d);
-        int leader = __ffs(peers) - 1;
-        uint32_t old = 0;
-        if (lane == leader) {
-            old = my_hist[d];
-            my_hist[d] = old + (uint32_t)__popc(peers);
+        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : pad_digit;
+        if (kBallot) {
+            unsigned int p = 0xffffffffu;
+#pragma unroll
+            for (int b = 0; b < 8; ++b) {
+                if (b < digit_bits) {  // warp-uniform
+                    const bool bit = d & (1 << b);
+                    const unsigned int vote = __ballot_sync(0xffffffffu, bit);
+                    p &= bit ? vote : ~vote;
+                }
+            }
+            peers[j] = p;
+        } else {
+            peers[j] = __match_any_sync(0xffffffffu, d);
         }
-        old = __shfl_sync(0xffffffffu, old, leader);
-        rank[j] = old + (uint32_t)__popc(peers & lanemask_lt);
-        __syncwarp();
+    }
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        int local = warp_first + j * 32 + lane;
+        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : pad_digit;
+        rank[j] = 0;
+        if ((peers[j] & lanemask_lt) == 0u) rank[j] = atomicAdd(&my_hist[d], (uint32_t)__popc(peers[j]));
+    }
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        rank[j] = __shfl_sync(0xffffffffu, rank[j], __ffs(peers[j]) - 1) +
+                  (uint32_t)__popc(peers[j] & lanemask_lt);
     }
     __syncthreads();
 
@@ -152,9 +193,9 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
         s_warp_hist[w * kRadix + tid] = block_count;
         block_count += c;
     }
-    // the padding items of the last tile sit in digit 255 and must not be published
+    // the padding items of the last tile sit in the largest digit and must not be published
     uint32_t publish_count = block_count;
-    if (tid == 255) publish_count -= (uint32_t)(kSortTile - valid);
+    if (tid == pad_digit) publish_count -= (uint32_t)(kSortTile - valid);
     gs_st_volatile_u32(status + tile * kRadix + tid,
                        (tile == 0 ? kStatPrefix : kStatAggregate) | publish_count);
 
@@ -176,25 +217,42 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
     __syncthreads();
 
     // ---- scatter the tile into shared memory in digit order -----------------------------------
+    // positions first (independent shared loads), stores second: the warp issues in order, so a
+    // load -> store chain per item would serialise the 16 items
 #pragma unroll
     for (int j = 0; j < kItems; ++j) {
         int local = warp_first + j * 32 + lane;
-        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : 255;
-        uint32_t pos = s_digit_base[d] + my_hist[d] + rank[j];
-        s_keys[pos] = key[j];
-        s_vals[pos] = val[j];
+        int d = (local < valid) ? (int)((compact_key(key[j], spec) >> shift) & 0xff) : pad_digit;
+        rank[j] += s_digit_base[d] + my_hist[d];
+    }
+#pragma unroll
+    for (int j = 0; j < kItems; ++j) {
+        s_keys[rank[j]] = key[j];
+        s_vals[rank[j]] = val[j];
     }
 
     // ---- decoupled look-back for digit `tid` -----------------------------------------------
     uint32_t excl = 0;
     if (tile > 0) {
+        // kLook predecessors are read at once (independent loads in flight) and then consumed
+        // in order; a word that is not published yet is polled on its own
+        constexpr int kLook = 8;
         long long b = tile - 1;
-        while (true) {
-            uint32_t s;
-            do { s = gs_ld_volatile_u32(status + b * kRadix + tid); } while ((s >> 30) == 0);
-            excl += s & kStatMask;
-            if ((s >> 30) == 2) break;
-            --b;
+        bool done = false;
+        while (!done) {
+            uint32_t w[kLook];
+#pragma unroll
+            for (int q = 0; q < kLook; ++q)
+                w[q] = (b - q >= 0) ? gs_ld_volatile_u32(status + (b - q) * kRadix + tid) : kStatPrefix;
+#pragma unroll
+            for (int q = 0; q < kLook; ++q) {
+                if (done) break;
+                uint32_t sw = w[q];
+                while ((sw >> 30) == 0) sw = gs_ld_volatile_u32(status + (b - q) * kRadix + tid);
+                excl += sw & kStatMask;
+                done = (sw >> 30) == 2;
+            }
+            b -= kLook;
         }
         gs_st_volatile_u32(status + tile * kRadix + tid, kStatPrefix | (excl + publish_count));
     }
@@ -202,12 +260,29 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
     __syncthreads();
 
     // ---- coalesced write-out: consecutive smem slots of one digit are consecutive in global -----
-    for (int i = tid; i < valid; i += kSortBlock) {
-        KeyT kk = s_keys[i];
-        int d = (int)((compact_key(kk, spec) >> shift) & 0xff);
-        uint32_t pos = (uint32_t)i + s_global_off[d];
-        keys_out[pos] = kk;
-        vals_out[pos] = s_vals[i];
+    // (loads of all 16 slots first, then the offsets, then the stores -- same reason as above)
+    {
+        KeyT kk[kItems];
+        int32_t vv[kItems];
+        uint32_t off[kItems];
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            const int i = tid + j * kSortBlock;
+            kk[j] = (i < valid) ? s_keys[i] : (KeyT)0;
+            vv[j] = (i < valid) ? s_vals[i] : 0;
+        }
+#pragma unroll
+        for (int j = 0; j < kItems; ++j)
+            off[j] = s_global_off[(int)((compact_key(kk[j], spec) >> shift) & 0xff)];
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            const int i = tid + j * kSortBlock;
+            if (i < valid) {
+                const uint32_t pos = (uint32_t)i + off[j];
+                keys_out[pos] = kk[j];
+                vals_out[pos] = vv[j];
+            }
+        }
     }
 }
 
@@ -225,9 +300,10 @@ inline int64_t sort_tiles(int64_t k) { return (k + kSortTile - 1) / kSortTile; }
 // ghist | gbase | tickets (64 B) | status[passes][tiles][256].
 template <typename KeyT>
 int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, int32_t *vals_a,
-              KeyT *keys_b, int32_t *vals_b, int64_t k, const KeySpec &spec, int num_passes,
+              KeyT *keys_b, int32_t *vals_b, int64_t k, const KeySpec &spec, int total_bits,
               void *workspace, cudaStream_t st)
 {
+    const int num_passes = (total_bits + 7) / 8;
     const int64_t tiles = sort_tiles(k);
     uint32_t *ghist = (uint32_t *)workspace;
     uint32_t *gbase = ghist + kMaxPasses * kRadix;
@@ -237,10 +313,16 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
     GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, used, st));
 
     static bool attr_set = false;  // one flag per KeyT instantiation
+    static bool ballot = true;
     if (!attr_set) {
-        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel<KeyT>,
+        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel<KeyT, false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sort_smem(sizeof(KeyT))));
+        GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel<KeyT, true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         (int)sort_smem(sizeof(KeyT))));
+        const char *e = getenv("GS_SORT_RANK");  // tuning knob: "match" or "ballot"
+        if (e) ballot = (e[0] == 'b');
         attr_set = true;
     }
 
@@ -256,9 +338,15 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
     for (int p = 0; p < num_passes; ++p) {
         KeyT *kout = (p & 1) ? keys_b : keys_a;
         int32_t *vout = (p & 1) ? vals_b : vals_a;
-        onesweep_kernel<KeyT><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
-            kin, vin, kout, vout, k, spec, 8 * p, gbase + p * kRadix,
-            status + (size_t)p * tiles * kRadix, tickets + p);
+        const int digit_bits = min(8, total_bits - 8 * p);
+        if (ballot)
+            onesweep_kernel<KeyT, true><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
+                kin, vin, kout, vout, k, spec, 8 * p, digit_bits, gbase + p * kRadix,
+                status + (size_t)p * tiles * kRadix, tickets + p);
+        else
+            onesweep_kernel<KeyT, false><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
+                kin, vin, kout, vout, k, spec, 8 * p, digit_bits, gbase + p * kRadix,
+                status + (size_t)p * tiles * kRadix, tickets + p);
         GS_LAUNCH_CHECK();
         kin = kout;
         vin = vout;
@@ -303,7 +391,7 @@ extern "C" int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt,
     if (num_passes == 0) return GS_OK;
     // pass 0 writes the alt buffers, pass 1 the primary ones, ...
     int rc = sort_impl<long long>((const long long *)keys, payload, (long long *)keys_alt, payload_alt,
-                                  (long long *)keys, payload, k, spec, num_passes, workspace,
+                                  (long long *)keys, payload, k, spec, depth_bits + tile_bits, workspace,
                                   (cudaStream_t)stream);
     if (rc != GS_OK) return rc;
     if (result_in_alt) *result_in_alt = (num_passes & 1);
@@ -322,7 +410,7 @@ extern "C" int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_
     KeySpec spec = {32, 0xffffffffull, 0ull};
     int num_passes = (key_bits + 7) / 8;
     int rc = sort_impl<unsigned int>(keys, payload, keys_alt, payload_alt, keys, payload, k, spec,
-                                     num_passes, workspace, (cudaStream_t)stream);
+                                     key_bits, workspace, (cudaStream_t)stream);
     if (rc != GS_OK) return rc;
     if (result_in_alt) *result_in_alt = (num_passes & 1);
     return GS_OK;
@@ -346,5 +434,5 @@ extern "C" int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int 
     int32_t *vals_a = (num_passes & 1) ? order : vals_tmp;
     int32_t *vals_b = (num_passes & 1) ? vals_tmp : order;
     return sort_impl<unsigned int>((const unsigned int *)depth_key, nullptr, keys_a, vals_a, keys_b,
-                                   vals_b, m, spec, num_passes, workspace, (cudaStream_t)stream);
+                                   vals_b, m, spec, depth_bits, workspace, (cudaStream_t)stream);
 }
