@@ -157,8 +157,10 @@ int gs_blend_bwd(int height, int width, const int32_t *tile_start, const int32_t
 /*
  * Per-point chain rule + SH band mask + factor scaling.  Replaces loop 2 of the backward kernel
  * (R.py:707-772), _clear_grad_by_color_max_sh_band (R.py:1167-1182) and the factor multiplies
- * (R.py:1105-1125).  grad_xyz [n,3] and grad_features [n,56] must be zero on entry; rows of the
- * m visible points are stored.  Optional hook outputs (may be null), all [m,...] in list order:
+ * (R.py:1105-1125).  With accumulate == 0, grad_xyz [n,3] and grad_features [n,56] must be zero on
+ * entry and the rows of the m visible points are stored; with accumulate != 0 those rows are added
+ * to what the buffers hold (several views summed into one gradient buffer, no zero fill per view).
+ * Optional hook outputs (may be null), all [m,...] in list order:
  * hook_grad_xyz [m,3], hook_grad_features [m,56], hook_grad_viewspace [m,2], hook_magnitude [m],
  * hook_num_affected [m] i32 (R.py:1127-1142).
  */
@@ -169,7 +171,7 @@ int gs_point_bwd(const float *xyz, const float *features, const int32_t *object_
                  float q_factor, float s_factor, float alpha_factor, float color_factor,
                  float high_order_color_factor, float *grad_xyz, float *grad_features,
                  float *hook_grad_xyz, float *hook_grad_features, float *hook_grad_viewspace,
-                 float *hook_magnitude, int32_t *hook_num_affected, void *stream);
+                 float *hook_magnitude, int32_t *hook_num_affected, int accumulate, void *stream);
 
 #ifdef __cplusplus
 }

@@ -176,6 +176,7 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
         super().__init__()
         self.config = config
         self.last_forward_info: Dict[str, object] = {}
+        self._accumulate_into = None
         outer = self
 
         class _module_function(torch.autograd.Function):
@@ -218,10 +219,29 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                         outer.config, ctx.state, pointcloud, pointcloud_features, point_object_id,
                         t_pointcloud_camera, ctx.camera_info, ctx.color_max_sh_band,
                         grad_rasterized_image, backward_valid_point_hook,
-                        GaussianPointCloudRasterisation.BackwardValidPointHookInput)
+                        GaussianPointCloudRasterisation.BackwardValidPointHookInput,
+                        accumulate_into=outer._accumulate_into)
                 return grad_pointcloud, grad_pointcloud_features, None, None, None, None, None, None
 
         self._module_function = _module_function
+
+    def accumulate_gradients_into(self, grad_point_cloud: Optional[torch.Tensor],
+                                  grad_point_cloud_features: Optional[torch.Tensor]) -> None:
+        """Extension for multi-view batches (not in the reference, which renders one view per step).
+
+        While set, every backward ADDS its point gradients into the two given float32 buffers
+        ([N,3] and [N,56], contiguous, zeroed by the caller once per batch) and returns no gradient
+        to autograd for those two inputs -- so a batch of views costs neither a zero fill nor an
+        AccumulateGrad pass per view.  Call with (None, None) to restore the reference behaviour.
+        """
+        if grad_point_cloud is None or grad_point_cloud_features is None:
+            self._accumulate_into = None
+            return
+        for t, cols in ((grad_point_cloud, 3), (grad_point_cloud_features, 56)):
+            if not (t.is_cuda and t.dtype == torch.float32 and t.dim() == 2 and t.shape[1] == cols
+                    and t.is_contiguous()):
+                raise ValueError("gradient buffers must be contiguous CUDA float32 [N,3] and [N,56]")
+        self._accumulate_into = (grad_point_cloud, grad_point_cloud_features)
 
     def forward(self, input_data: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput"):
         camera_info = input_data.camera_info
@@ -421,13 +441,18 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
 
 def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, point_object_id,
                    t_pointcloud_camera, camera_info, color_max_sh_band, grad_rasterized_image,
-                   hook, hook_input_type):
+                   hook, hook_input_type, accumulate_into=None):
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
     stream = torch.cuda.current_stream(dev).cuda_stream
     _mark("backward_begin")
-    grad_pointcloud = torch.zeros_like(pointcloud)
-    grad_features = torch.zeros_like(pointcloud_features, memory_format=torch.contiguous_format)
+    if accumulate_into is not None:
+        grad_pointcloud, grad_features = accumulate_into
+        if grad_pointcloud.shape[0] != n or grad_features.shape[0] != n:
+            raise ValueError("accumulation buffers do not match the point cloud")
+    else:
+        grad_pointcloud = torch.zeros_like(pointcloud)
+        grad_features = torch.zeros_like(pointcloud_features, memory_format=torch.contiguous_format)
     if grad_rasterized_image is None:
         grad_rasterized_image = torch.zeros(H, W, 3, dtype=torch.float32, device=dev)
     g_img = grad_rasterized_image.detach().to(torch.float32).contiguous()
@@ -459,7 +484,8 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
             float(cfg.grad_q_factor), float(cfg.grad_s_factor), float(cfg.grad_alpha_factor),
             float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
             grad_pointcloud.data_ptr(), grad_features.data_ptr(), _ptr(h_xyz), _ptr(h_feat),
-            _ptr(h_view), _ptr(h_mag), _ptr(h_aff), stream), "gs_point_bwd")
+            _ptr(h_view), _ptr(h_mag), _ptr(h_aff), int(accumulate_into is not None), stream),
+            "gs_point_bwd")
     _mark("point_bwd")
     if want_hook:
         point_in_camera = buf.view("point_in_camera", m)
@@ -475,6 +501,8 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
             point_depth=point_in_camera[:, 2],
             point_uv_in_camera=buf.view("point_uv", m),
         ))
+    if accumulate_into is not None:
+        return None, None  # already added into the caller's buffers
     return grad_pointcloud, grad_features
 
 

@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
 
-ABI_VERSION = 101
+ABI_VERSION = 102
 
 _p = C.c_void_p
 _i = C.c_int
@@ -43,7 +43,7 @@ SIGNATURES = {
     "gs_blend_fwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "gs_blend_bwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "gs_point_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p, _p, _i, _f, _f, _f, _f, _f,
-                          _p, _p, _p, _p, _p, _p, _p, _p]),
+                          _p, _p, _p, _p, _p, _p, _p, _i, _p]),
 }
 
 

@@ -27,6 +27,7 @@ struct PointBwdParams {
     const float *point_in_camera;
     const float *splat_grads;
     int keep;  // SH coefficients kept per channel: 1, 4, 9 or 16
+    int accumulate;  // add into grad_xyz / grad_features instead of storing
     float q_factor, s_factor, alpha_factor, color_factor, high_order_color_factor;
     float *grad_xyz;
     float *grad_features;
@@ -36,6 +37,16 @@ struct PointBwdParams {
     float *hook_magnitude;
     int32_t *hook_num_affected;
 };
+
+__device__ __forceinline__ void put4(float4 *dst, const float4 &v, bool accumulate)
+{
+    if (accumulate) {
+        const float4 o = *dst;
+        *dst = make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w);
+    } else {
+        *dst = v;
+    }
+}
 
 __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
 {
@@ -137,8 +148,8 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
                                       gq[3] * p.q_factor);
         const float4 o1 = make_float4(gs3[0] * p.s_factor, gs3[1] * p.s_factor, gs3[2] * p.s_factor,
                                       glogit * p.alpha_factor);
-        grow[0] = o0;
-        grow[1] = o1;
+        put4(grow, o0, p.accumulate);
+        put4(grow + 1, o1, p.accumulate);
         if (hrow) { hrow[0] = o0; hrow[1] = o1; }
     }
 #pragma unroll
@@ -162,13 +173,19 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
                 o[e] = (k < p.keep) ? scale * basis[k] * f : 0.0f;
             }
             const float4 o4 = make_float4(o[0], o[1], o[2], o[3]);
-            grow[2 + 4 * ch + k4] = o4;
+            put4(grow + 2 + 4 * ch + k4, o4, p.accumulate);
             if (hrow) hrow[2 + 4 * ch + k4] = o4;
         }
     }
-    p.grad_xyz[3 * pid] = gxyz[0];
-    p.grad_xyz[3 * pid + 1] = gxyz[1];
-    p.grad_xyz[3 * pid + 2] = gxyz[2];
+    if (p.accumulate) {
+        p.grad_xyz[3 * pid] += gxyz[0];
+        p.grad_xyz[3 * pid + 1] += gxyz[1];
+        p.grad_xyz[3 * pid + 2] += gxyz[2];
+    } else {
+        p.grad_xyz[3 * pid] = gxyz[0];
+        p.grad_xyz[3 * pid + 1] = gxyz[1];
+        p.grad_xyz[3 * pid + 2] = gxyz[2];
+    }
 
     if (p.hook_grad_xyz) {
         p.hook_grad_xyz[3 * idx] = gxyz[0];
@@ -193,7 +210,8 @@ extern "C" int gs_point_bwd(const float *xyz, const float *features, const int32
                             float alpha_factor, float color_factor, float high_order_color_factor,
                             float *grad_xyz, float *grad_features, float *hook_grad_xyz,
                             float *hook_grad_features, float *hook_grad_viewspace,
-                            float *hook_magnitude, int32_t *hook_num_affected, void *stream)
+                            float *hook_magnitude, int32_t *hook_num_affected, int accumulate,
+                            void *stream)
 {
     if (m < 0 || n_obj <= 0) return GS_E_INVALID;
     if (m == 0) return GS_OK;
@@ -211,6 +229,7 @@ extern "C" int gs_point_bwd(const float *xyz, const float *features, const int32
     p.hook_grad_xyz = hook_grad_xyz; p.hook_grad_features = hook_grad_features;
     p.hook_grad_viewspace = hook_grad_viewspace; p.hook_magnitude = hook_magnitude;
     p.hook_num_affected = hook_num_affected;
+    p.accumulate = accumulate;
     int threads = 128;
     long long blocks = (m + threads - 1) / threads;
     point_bwd_kernel<<<(unsigned)blocks, threads, 0, (cudaStream_t)stream>>>(p);

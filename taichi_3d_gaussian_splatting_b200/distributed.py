@@ -41,11 +41,18 @@ class ViewShardedTrainerStep:
 
     def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
                  loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
-                 group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True):
+                 group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True,
+                 rasteriser: Any = None):
+        """rasteriser: the GaussianPointCloudRasterisation module `render` calls, if the step should
+        use its fused accumulation (`accumulate_gradients_into`): every view's backward then adds
+        into one flat N x 59 buffer (no per-view zero fill, no AccumulateGrad pass) and the exchange
+        is ONE all-reduce of that buffer."""
         self.render = render
         self.loss_fn = loss_fn
         self.group = group
         self.sync_quaternions = sync_quaternions
+        self.rasteriser = rasteriser
+        self._flat: Optional[torch.Tensor] = None
 
     def _world(self):
         if dist.is_available() and dist.is_initialized():
@@ -65,11 +72,29 @@ class ViewShardedTrainerStep:
         point_cloud_features.grad = None
         mine = views_of_rank(len(views), rank, world)
         total = torch.zeros((), dtype=torch.float32, device=point_cloud.device)
-        for v in mine:
-            image = self.render(point_cloud, point_cloud_features, views[v])
-            loss = self.loss_fn(image, views[v])
-            loss.backward()          # accumulates into .grad across this rank's views
-            total = total + loss.detach()
+        fused = self.rasteriser is not None
+        if fused:
+            n = point_cloud.shape[0]
+            if self._flat is None or self._flat.numel() != n * 59 or self._flat.device != point_cloud.device:
+                self._flat = torch.empty(n * 59, dtype=torch.float32, device=point_cloud.device)
+            self._flat.zero_()
+            gx, gf = self._flat[:3 * n].view(n, 3), self._flat[3 * n:].view(n, 56)
+            self.rasteriser.accumulate_gradients_into(gx, gf)
+        try:
+            for v in mine:
+                image = self.render(point_cloud, point_cloud_features, views[v])
+                loss = self.loss_fn(image, views[v])
+                loss.backward()          # accumulates across this rank's views
+                total = total + loss.detach()
+        finally:
+            if fused:
+                self.rasteriser.accumulate_gradients_into(None, None)
+        if fused:
+            if world > 1:
+                dist.all_reduce(self._flat, group=self.group)
+                dist.all_reduce(total, group=self.group)
+            point_cloud.grad, point_cloud_features.grad = gx, gf
+            return StepResult(loss=total, num_local_views=len(mine))
         # a rank with no view of this batch still takes part in the exchange with zeros
         if point_cloud.grad is None:
             point_cloud.grad = torch.zeros_like(point_cloud)

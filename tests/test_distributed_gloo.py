@@ -79,3 +79,75 @@ def test_two_rank_step_matches_single_process():
     assert not torch.equal(out[0][3][:, :4], out[1][3][:, :4])
     # ... and step 2's losses agree exactly because the q columns are re-broadcast first
     assert torch.equal(out[2][1], out[3][1])
+
+
+class _FusedStub:
+    """Stand-in for the rasteriser's fused accumulation (`accumulate_gradients_into`): a view's
+    backward adds its gradient into the caller's buffers and hands autograd nothing."""
+
+    def __init__(self):
+        self.buffers = None
+        stub = self
+
+        class _Fn(torch.autograd.Function):
+            @staticmethod
+            def forward(ctx, xyz, feat, view):
+                ctx.view = view
+                ctx.save_for_backward(xyz, feat)
+                with torch.enable_grad():
+                    pass
+                return _render(xyz.detach(), feat.detach(), view)
+
+            @staticmethod
+            def backward(ctx, g):
+                xyz, feat = ctx.saved_tensors
+                with torch.enable_grad():
+                    x = xyz.detach().requires_grad_(True)
+                    f = feat.detach().clone().requires_grad_(True)
+                    gx, gf = torch.autograd.grad(_render(x, f, ctx.view), (x, f), g)
+                if stub.buffers is None:
+                    return gx, gf, None
+                stub.buffers[0].add_(gx)
+                stub.buffers[1].add_(gf)
+                return None, None, None
+
+        self.fn = _Fn
+
+    def accumulate_gradients_into(self, gx, gf):
+        self.buffers = None if gx is None else (gx, gf)
+
+    def render(self, xyz, feat, view):
+        return self.fn.apply(xyz, feat, view)
+
+
+def _fused_worker(rank, world, port, n, views, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.manual_seed(0)
+    xyz = torch.randn(n, 3, requires_grad=True)
+    feat = torch.randn(n, 56, requires_grad=True)
+    stub = _FusedStub()
+    step = ViewShardedTrainerStep(stub.render, _loss, rasteriser=stub)
+    res = step(xyz, feat, views)
+    assert stub.buffers is None  # accumulation mode is switched off again after the step
+    out[rank] = (xyz.grad.clone(), feat.grad.clone(), res.loss.clone())
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_two_rank_fused_accumulation_matches_plain_step():
+    n, views, world = 150, list(range(6)), 2
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_fused_worker, args=(world, _free_port(), n, views, out), nprocs=world, join=True)
+        out = dict(out)
+    torch.manual_seed(0)
+    xyz = torch.randn(n, 3, requires_grad=True)
+    feat = torch.randn(n, 56, requires_grad=True)
+    res = ViewShardedTrainerStep(_render, _loss)(xyz, feat, views)
+    for r in range(world):
+        gx, gf, loss = out[r]
+        assert torch.allclose(gx, xyz.grad, rtol=1e-5, atol=1e-5)
+        assert torch.allclose(gf, feat.grad, rtol=1e-4, atol=1e-4)
+        assert torch.allclose(loss, res.loss, rtol=1e-5)
+    assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1])

@@ -383,3 +383,35 @@ def test_full_size_c2_against_oracle(oracle32, oracle64):
         l2, mx = util.grad_error(o64, cuda)
         print(f"C2 grad {name}: rel-l2 {l2:.2e} max-col-norm {mx:.2e}")
         assert l2 <= 1e-4 and mx <= 1e-4
+
+
+def test_accumulate_gradients_into_sums_views():
+    """Extension for multi-view batches: backward adds into caller buffers; equals the sum of the
+    per-view gradients autograd would have produced."""
+    scene = make_scene(5000, 128, 96, seed=21, scale_factor=0.03)
+    g = torch.from_numpy(np.random.default_rng(2).uniform(0, 1, (96, 128, 3)).astype(np.float32)).cuda()
+    poses = [(0.0, 0.0), (0.02, -0.01), (-0.03, 0.02)]
+    ras = _module()
+
+    def run(t, dx, dy):
+        t["t_pointcloud_camera"] = torch.tensor([[dx, dy, 0.0]], device="cuda")
+        image, _, _ = _call(ras, scene, t, band=3)
+        (image * g).sum().backward()
+
+    ref = util.scene_tensors(scene, requires_grad=True)
+    for dx, dy in poses:                       # plain autograd accumulation
+        run(ref, dx, dy)
+    t = util.scene_tensors(scene, requires_grad=True)
+    n = t["point_cloud"].shape[0]
+    gx = torch.zeros(n, 3, device="cuda")
+    gf = torch.zeros(n, 56, device="cuda")
+    ras.accumulate_gradients_into(gx, gf)
+    for dx, dy in poses:
+        run(t, dx, dy)
+    ras.accumulate_gradients_into(None, None)
+    assert t["point_cloud"].grad is None and t["point_cloud_features"].grad is None
+    for got, want in ((gx, ref["point_cloud"].grad), (gf, ref["point_cloud_features"].grad)):
+        l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
+        assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
+    with pytest.raises(ValueError):
+        ras.accumulate_gradients_into(gx[:, :2], gf)
