@@ -17,6 +17,14 @@ def main():
     def get(r, name, default=""):
         return r[col[name]] if name in col else default
 
+    units = rows[1]
+    scale = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}
+    tscale = scale.get(units[col["gpu__time_duration.sum"]], 1.0) if "gpu__time_duration.sum" in col else 1.0
+    bscale = {"byte": 1e-6, "Kbyte": 1e-3, "Mbyte": 1.0, "Gbyte": 1e3}
+
+    def mb(r, name):
+        return float(get(r, name) or 0) * bscale.get(units[col[name]], 1.0) if name in col else 0.0
+
     stall_cols = [c for c in h if c.startswith("smsp__average_warps_issue_stalled_") and c.endswith("_per_issue_active.ratio")]
     lines = []
     for r in rows[2:]:
@@ -25,8 +33,8 @@ def main():
         stalls = [(v, n) for v, n in stalls if n not in ("selected",)][:4]
         rec = dict(
             kernel=name, grid=get(r, "Grid Size"), block=get(r, "Block Size"),
-            ms=float(get(r, "gpu__time_duration.sum") or 0),
-            dram_rd_mb=float(get(r, "dram__bytes_read.sum") or 0), dram_wr_mb=float(get(r, "dram__bytes_write.sum") or 0),
+            ms=float(get(r, "gpu__time_duration.sum") or 0) * tscale,
+            dram_rd_mb=mb(r, "dram__bytes_read.sum"), dram_wr_mb=mb(r, "dram__bytes_write.sum"),
             dram_pct=float(get(r, "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed") or 0),
             minst=float(get(r, "smsp__inst_executed.sum") or 0) / 1e6,
             issue_pct=float(get(r, "smsp__issue_active.avg.pct_of_peak_sustained_active") or 0),
