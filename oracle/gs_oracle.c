@@ -41,7 +41,7 @@
  * tests/GaussianPoint3D_test.py:12-54, single point alpha/grads T_R.py:353-548,
  * pose inverse tests/utils_test.py:138-157) and against fixtures produced by
  * executing the reference's Python source under a numpy-float32 Taichi shim
- * (tests/golden/gen_golden.py).  Against Taichi's real CUDA code generation the
+ * (tests/golden/gen_golden.py, tests/test_reference_golden.py).  Against Taichi's real CUDA code generation the
  * parity is unpinned (Taichi cannot be installed in the build container).
  *
  * A second build with -DGSO_DOUBLE makes every `real` a double and uses libm
