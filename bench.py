@@ -39,6 +39,8 @@ WORKLOADS = {
     "c2_1m_1920x1088": (1_000_000, 1920, 1088, 0.004, 1002),
     "c3_430k_976x544": (430_000, 976, 544, 0.004, 1003),
     "small_100k_976x544": (100_000, 976, 544, 0.004, 1005),
+    "c4_2m_976x544": (2_000_000, 976, 544, 0.004, 1004),
+    "c5_5m_3840x2160": (5_000_000, 3840, 2160, 0.004, 1006),
 }
 METRIC = "fwd+bwd iters/s"  # BASELINE.json metric, first half; render Mpix/s rides along as render_mpix_per_s
 NUM_VIEWS = 8

@@ -48,12 +48,13 @@ __device__ __forceinline__ void put4(float4 *dst, const float4 &v, bool accumula
     }
 }
 
-__global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
+constexpr int kRowStride4 = 15;  // float4 per staged row: 14 used + 1 pad (240 B: conflict-free 16-byte lanes)
+
+// Chain rule of one visible point.  `row` is the point's 56-float feature row staged in shared
+// memory; it is overwritten IN PLACE with the row of feature gradients (already masked / scaled).
+__device__ __forceinline__ void point_chain(const PointBwdParams &p, long long idx, long long pid,
+                                            float4 *row)
 {
-    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= p.m) return;
-    const long long pid = p.ids[idx];
-    const float4 *row = reinterpret_cast<const float4 *>(p.features + (size_t)GS_FEATURES * pid);
     const float4 *sg4 = reinterpret_cast<const float4 *>(p.splat_grads + (size_t)kGradSlots * idx);
     const float4 ga = __ldg(sg4), gb = __ldg(sg4 + 1), gc = __ldg(sg4 + 2);
     const float gu = ga.x, gv = ga.y, c00 = ga.z, c01 = ga.w, c11 = gb.x;
@@ -139,18 +140,14 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
     float basis[16];
     gs_sh_basis(px - __ldg(org), py - __ldg(org + 1), pz - __ldg(org + 2), basis);
 
-    float4 *grow = reinterpret_cast<float4 *>(p.grad_features + (size_t)GS_FEATURES * pid);
-    float4 *hrow = p.hook_grad_features
-                       ? reinterpret_cast<float4 *>(p.hook_grad_features + (size_t)GS_FEATURES * idx)
-                       : nullptr;
+    float4 *grow = row;
     {
         const float4 o0 = make_float4(gq[0] * p.q_factor, gq[1] * p.q_factor, gq[2] * p.q_factor,
                                       gq[3] * p.q_factor);
         const float4 o1 = make_float4(gs3[0] * p.s_factor, gs3[1] * p.s_factor, gs3[2] * p.s_factor,
                                       glogit * p.alpha_factor);
-        put4(grow, o0, p.accumulate);
-        put4(grow + 1, o1, p.accumulate);
-        if (hrow) { hrow[0] = o0; hrow[1] = o1; }
+        grow[0] = o0;
+        grow[1] = o1;
     }
 #pragma unroll
     for (int ch = 0; ch < 3; ++ch) {
@@ -173,8 +170,7 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
                 o[e] = (k < p.keep) ? scale * basis[k] * f : 0.0f;
             }
             const float4 o4 = make_float4(o[0], o[1], o[2], o[3]);
-            put4(grow + 2 + 4 * ch + k4, o4, p.accumulate);
-            if (hrow) hrow[2 + 4 * ch + k4] = o4;
+            grow[2 + 4 * ch + k4] = o4;  // the channel's coefficients were all read above
         }
     }
     if (p.accumulate) {
@@ -198,6 +194,43 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
     }
     if (p.hook_magnitude) p.hook_magnitude[idx] = gmag;
     if (p.hook_num_affected) p.hook_num_affected[idx] = (int32_t)gcount;
+}
+
+// One thread per visible point for the arithmetic; the 224-byte feature rows in and the 224-byte
+// gradient rows out move through shared memory so that every global access is a coalesced run:
+// a half warp handles one row per instruction (14 lanes x 16 B), two rows per instruction.
+__global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
+{
+    __shared__ float4 s_rows[4][32 * kRowStride4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = idx < p.m;
+    const long long pid = valid ? (long long)p.ids[idx] : -1;
+    float4 *rows = s_rows[warp];
+    const int half = lane >> 4, col = lane & 15;
+
+#pragma unroll 4
+    for (int r = 0; r < 32; r += 2) {
+        const long long rpid = __shfl_sync(0xffffffffu, pid, r + half);
+        if (col < 14 && rpid >= 0)
+            rows[(r + half) * kRowStride4 + col] =
+                __ldg(reinterpret_cast<const float4 *>(p.features + (size_t)GS_FEATURES * rpid) + col);
+    }
+    __syncwarp();
+    if (valid) point_chain(p, idx, pid, rows + lane * kRowStride4);
+    __syncwarp();
+    const long long idx0 = idx - lane;
+#pragma unroll 4
+    for (int r = 0; r < 32; r += 2) {
+        const long long rpid = __shfl_sync(0xffffffffu, pid, r + half);
+        if (col < 14 && rpid >= 0) {
+            const float4 v = rows[(r + half) * kRowStride4 + col];
+            put4(reinterpret_cast<float4 *>(p.grad_features + (size_t)GS_FEATURES * rpid) + col, v,
+                 p.accumulate);
+            if (p.hook_grad_features)
+                reinterpret_cast<float4 *>(p.hook_grad_features + (size_t)GS_FEATURES * (idx0 + r + half))[col] = v;
+        }
+    }
 }
 
 }  // namespace

@@ -79,8 +79,54 @@ __device__ __forceinline__ float dot16(const float *f, const float *b)
     return s;
 }
 
+// ---- bulk (TMA) staging of the feature rows ---------------------------------------------------
+// The 32 points of a warp own 32 consecutive 224-byte rows = one contiguous 7168-byte run of
+// point_cloud_features: one elected lane fetches it with a single cp.async.bulk (UBLKCP) into
+// shared memory, completion tracked by an mbarrier, while the warp does the cull arithmetic.
+constexpr int kRowBytes = GS_FEATURES * 4;          // 224
+constexpr int kWarpRowBytes = 32 * kRowBytes;       // 7168
+constexpr int kProjWarps = kProjBlock / 32;
+constexpr size_t kProjSmem = (size_t)kProjWarps * kWarpRowBytes + kProjWarps * 8;
+
+__device__ __forceinline__ void mbar_init(unsigned long long *bar, unsigned count)
+{
+    unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_load(void *dst_smem, const void *src, unsigned bytes,
+                                          unsigned long long *bar)
+{
+    unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+    unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(b), "r"(bytes) : "memory");
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(d),
+        "l"(src), "r"(bytes), "r"(b)
+        : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(b),
+        "r"(parity)
+        : "memory");
+}
+
+// kBulk: feature rows come through shared memory by cp.async.bulk (needs a 16-byte aligned
+// features pointer); otherwise every thread reads its own row from global memory.
+template <bool kBulk>
 __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectParams p)
 {
+    extern __shared__ __align__(128) unsigned char s_dyn[];
     __shared__ unsigned int s_ticket;
     __shared__ unsigned long long s_warp_total[kProjBlock / 32];
     __shared__ unsigned long long s_block_excl;
@@ -90,6 +136,19 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     __syncthreads();
     const int block = (int)s_ticket;
     const long long i = (long long)block * kProjBlock + tid;
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(s_dyn + (size_t)kProjWarps * kWarpRowBytes) + warp;
+    const float4 *s_row = reinterpret_cast<const float4 *>(s_dyn + (size_t)warp * kWarpRowBytes) + 14 * lane;
+    if (kBulk) {
+        const long long i0 = i - lane;
+        const long long rows = min(32ll, p.n - i0);
+        if (lane == 0) {
+            mbar_init(bar, 1);
+            if (rows > 0)
+                bulk_load(s_dyn + (size_t)warp * kWarpRowBytes, p.features + (size_t)GS_FEATURES * i0,
+                          (unsigned)(rows * kRowBytes), bar);
+        }
+        __syncwarp();
+    }
 
     // ---- cull (R.py:50-78) -------------------------------------------------------------
     bool visible = false;
@@ -123,15 +182,17 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     float conic0 = 0.f, conic1 = 0.f, conic2 = 0.f, rescale = 0.f, alpha = 0.f;
     float col0 = 0.f, col1 = 0.f, col2 = 0.f, radius = 0.f;
     int tu0 = 0, tu1 = 0, tv0 = 0, tv1 = 0, count = 0;
+    if (kBulk && i - lane < p.n) mbar_wait(bar, 0);  // every warp that issued a copy waits for it
     if (visible) {
-        float4 *row = reinterpret_cast<float4 *>(p.features + (size_t)GS_FEATURES * i);
+        float4 *grow = reinterpret_cast<float4 *>(p.features + (size_t)GS_FEATURES * i);
+        const float4 *row = kBulk ? s_row : grow;
         float4 q4 = row[0];
         float4 s4 = row[1];
         // normalise the quaternion in place (R.py:196-205)
         float n2 = ((q4.x * q4.x + q4.y * q4.y) + q4.z * q4.z) + q4.w * q4.w;
         float invlen = 1.0f / sqrtf(n2);
         q4.x = invlen * q4.x; q4.y = invlen * q4.y; q4.z = invlen * q4.z; q4.w = invlen * q4.w;
-        row[0] = q4;
+        grow[0] = q4;
 
         // Sigma' = J W Sigma W^T J^T (reference GaussianPoint3D.py:162-191)
         float fx = K[0], fy = K[4];
@@ -355,7 +416,17 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
     p.status = (unsigned long long *)workspace;
     p.ticket = (unsigned int *)((unsigned long long *)workspace + blocks);
     GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, (size_t)gs_project_workspace_bytes(n), st));
-    project_cull_sh_kernel<<<blocks, kProjBlock, 0, st>>>(p);
+    if (((uintptr_t)features % 16) == 0) {
+        static bool attr_set = false;
+        if (!attr_set) {
+            GS_CUDA_TRY(cudaFuncSetAttribute(project_cull_sh_kernel<true>,
+                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kProjSmem));
+            attr_set = true;
+        }
+        project_cull_sh_kernel<true><<<blocks, kProjBlock, kProjSmem, st>>>(p);
+    } else {
+        project_cull_sh_kernel<false><<<blocks, kProjBlock, 0, st>>>(p);
+    }
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
