@@ -183,11 +183,16 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     float col0 = 0.f, col1 = 0.f, col2 = 0.f, radius = 0.f;
     int tu0 = 0, tu1 = 0, tv0 = 0, tv1 = 0, count = 0;
     if (kBulk && i - lane < p.n) mbar_wait(bar, 0);  // every warp that issued a copy waits for it
+    // Phase 1: what the tile count needs (covariance -> radius -> bounding box).  The block's
+    // aggregate is published right after it, so the look-back of this and of later blocks overlaps
+    // phase 2 (conic, opacity, SH colour) instead of stalling the block at a barrier.
+    float4 *grow = reinterpret_cast<float4 *>(p.features + (size_t)GS_FEATURES * i);
+    const float4 *row = kBulk ? s_row : grow;
+    float4 s4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    float c00 = 0.f, c01 = 0.f, c10 = 0.f, c11 = 0.f;
     if (visible) {
-        float4 *grow = reinterpret_cast<float4 *>(p.features + (size_t)GS_FEATURES * i);
-        const float4 *row = kBulk ? s_row : grow;
         float4 q4 = row[0];
-        float4 s4 = row[1];
+        s4 = row[1];
         // normalise the quaternion in place (R.py:196-205)
         float n2 = ((q4.x * q4.x + q4.y * q4.y) + q4.z * q4.z) + q4.w * q4.w;
         float invlen = 1.0f / sqrtf(n2);
@@ -229,11 +234,53 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
             for (int c = 0; c < 3; ++c)
                 X[3 * r + c] = (V[3 * r] * W[3 * c] + V[3 * r + 1] * W[3 * c + 1]) +
                                V[3 * r + 2] * W[3 * c + 2];
-        float c00 = X[0] * J0 + X[2] * J2;
-        float c01 = X[1] * J4 + X[2] * J5;
-        float c10 = X[3] * J0 + X[5] * J2;
-        float c11 = X[4] * J4 + X[5] * J5;
+        c00 = X[0] * J0 + X[2] * J2;
+        c01 = X[1] * J4 + X[2] * J5;
+        c10 = X[3] * J0 + X[5] * J2;
+        c11 = X[4] * J4 + X[5] * J5;
 
+        // radius from the unfiltered covariance (R.py:311-315)
+        float lam = (c00 + c11 + sqrtf((c00 - c11) * (c00 - c11) + 4.0f * c01 * c10)) / 2.0f;
+        radius = sqrtf(lam) * 3.0f;
+
+        // tile bounding box (R.py:81-103); non-finite splats get an empty box
+        if (isfinite(u) && isfinite(v) && isfinite(radius)) {
+            float r = fmaxf(radius, 1.0f);
+            float min_u = fmaxf(0.0f, u - r), max_u = u + r;
+            float min_v = fmaxf(0.0f, v - r), max_v = v + r;
+            int tw = p.width / kTile, th = p.height / kTile;
+            const float cap = 1.0e9f;
+            tu0 = min((int)fminf(floorf(min_u / kTile), cap), tw);
+            tu1 = min(max((int)fminf(floorf(max_u / kTile), cap) + 1, tu0 + 1), tw);
+            tv0 = min((int)fminf(floorf(min_v / kTile), cap), th);
+            tv1 = min(max((int)fminf(floorf(max_v / kTile), cap) + 1, tv0 + 1), th);
+        }
+        count = (tu1 - tu0) * (tv1 - tv0);
+    }
+
+
+    // ---- ordered compaction, part 1: block scan, publish the block aggregate ----------------
+    unsigned long long mine = ((unsigned long long)(visible ? 1u : 0u) << 32) | (unsigned int)count;
+    unsigned long long incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += o;
+    }
+    if (lane == 31) s_warp_total[warp] = incl;
+    __syncthreads();
+    unsigned long long warp_excl = 0, block_total = 0;
+#pragma unroll
+    for (int w = 0; w < kProjBlock / 32; ++w) {
+        unsigned long long t = s_warp_total[w];
+        if (w < warp) warp_excl += t;
+        block_total += t;
+    }
+    if (tid == 0)
+        gs_st_volatile_u64(p.status + block, (block == 0 ? kFlagPrefix : kFlagAggregate) | block_total);
+
+    // Phase 2: the rest of the per-point attributes (R.py:286-310)
+    if (visible) {
         // conic + rescale on a by-value copy (reference utils.py:257-272)
         {
             float det0 = c00 * c11 - c01 * c10;
@@ -266,46 +313,10 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
             if (ch == 0) col0 = c; else if (ch == 1) col1 = c; else col2 = c;
         }
 
-        // radius from the unfiltered covariance (R.py:311-315)
-        float lam = (c00 + c11 + sqrtf((c00 - c11) * (c00 - c11) + 4.0f * c01 * c10)) / 2.0f;
-        radius = sqrtf(lam) * 3.0f;
-
-        // tile bounding box (R.py:81-103); non-finite splats get an empty box
-        if (isfinite(u) && isfinite(v) && isfinite(radius)) {
-            float r = fmaxf(radius, 1.0f);
-            float min_u = fmaxf(0.0f, u - r), max_u = u + r;
-            float min_v = fmaxf(0.0f, v - r), max_v = v + r;
-            int tw = p.width / kTile, th = p.height / kTile;
-            const float cap = 1.0e9f;
-            tu0 = min((int)fminf(floorf(min_u / kTile), cap), tw);
-            tu1 = min(max((int)fminf(floorf(max_u / kTile), cap) + 1, tu0 + 1), tw);
-            tv0 = min((int)fminf(floorf(min_v / kTile), cap), th);
-            tv1 = min(max((int)fminf(floorf(max_v / kTile), cap) + 1, tv0 + 1), th);
-        }
-        count = (tu1 - tu0) * (tv1 - tv0);
     }
 
-    // ---- ordered compaction: block scan + decoupled look-back over blocks ---------------
-    unsigned long long mine = ((unsigned long long)(visible ? 1u : 0u) << 32) | (unsigned int)count;
-    unsigned long long incl = mine;
-#pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += o;
-    }
-    if (lane == 31) s_warp_total[warp] = incl;
-    __syncthreads();
-    unsigned long long warp_excl = 0, block_total = 0;
-#pragma unroll
-    for (int w = 0; w < kProjBlock / 32; ++w) {
-        unsigned long long t = s_warp_total[w];
-        if (w < warp) warp_excl += t;
-        block_total += t;
-    }
+    // ---- ordered compaction, part 2: decoupled look-back over blocks -------------------------
     if (warp == 0) {
-        if (lane == 0)
-            gs_st_volatile_u64(p.status + block,
-                               (block == 0 ? kFlagPrefix : kFlagAggregate) | block_total);
         unsigned long long excl = 0;
         if (block > 0) {
             int base = block - 1;
