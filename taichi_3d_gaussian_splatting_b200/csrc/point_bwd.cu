@@ -38,11 +38,14 @@ struct PointBwdParams {
     int32_t *hook_num_affected;
 };
 
+// store, or add without reading back: one 16-byte vector reduction resolved in L2 (rows are
+// unique within a launch, so there is no contention; the SM never waits for the old value)
 __device__ __forceinline__ void put4(float4 *dst, const float4 &v, bool accumulate)
 {
     if (accumulate) {
-        const float4 o = *dst;
-        *dst = make_float4(o.x + v.x, o.y + v.y, o.z + v.z, o.w + v.w);
+        asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst), "f"(v.x), "f"(v.y),
+                     "f"(v.z), "f"(v.w)
+                     : "memory");
     } else {
         *dst = v;
     }
@@ -174,9 +177,9 @@ __device__ __forceinline__ void point_chain(const PointBwdParams &p, long long i
         }
     }
     if (p.accumulate) {
-        p.grad_xyz[3 * pid] += gxyz[0];
-        p.grad_xyz[3 * pid + 1] += gxyz[1];
-        p.grad_xyz[3 * pid + 2] += gxyz[2];
+        atomicAdd(p.grad_xyz + 3 * pid, gxyz[0]);
+        atomicAdd(p.grad_xyz + 3 * pid + 1, gxyz[1]);
+        atomicAdd(p.grad_xyz + 3 * pid + 2, gxyz[2]);
     } else {
         p.grad_xyz[3 * pid] = gxyz[0];
         p.grad_xyz[3 * pid + 1] = gxyz[1];
@@ -209,7 +212,7 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
     float4 *rows = s_rows[warp];
     const int half = lane >> 4, col = lane & 15;
 
-#pragma unroll 4
+#pragma unroll 8
     for (int r = 0; r < 32; r += 2) {
         const long long rpid = __shfl_sync(0xffffffffu, pid, r + half);
         if (col < 14 && rpid >= 0)
@@ -220,7 +223,7 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
     if (valid) point_chain(p, idx, pid, rows + lane * kRowStride4);
     __syncwarp();
     const long long idx0 = idx - lane;
-#pragma unroll 4
+#pragma unroll 8
     for (int r = 0; r < 32; r += 2) {
         const long long rpid = __shfl_sync(0xffffffffu, pid, r + half);
         if (col < 14 && rpid >= 0) {
