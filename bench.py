@@ -231,7 +231,7 @@ def run_reference(args):
         "note": "reference's Taichi kernels unavailable on this box (no taichi wheel); CPU oracle "
                 "= C restatement of the same path, OpenMP over points/tiles",
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def run_b200(args):
@@ -459,13 +459,34 @@ def run_b200(args):
         "gpu_launches": launches_per_step * VIEWS_PER_RANK * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "stages": stages,
     }
-    print(json.dumps(line), flush=True)
+    _emit(line)
     if world > 1:
         dist.destroy_process_group()
 
 
 def main():
     args = parse_args()
+    # stdout carries exactly one JSON line: anything libraries print there meanwhile (NCCL's version
+    # banner, for one) is sent to stderr
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    try:
+        _run(args)
+    finally:
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+    if _LINE:
+        print(_LINE[0], flush=True)
+
+
+_LINE = []
+
+
+def _emit(line: dict) -> None:
+    _LINE.append(json.dumps(line))
+
+
+def _run(args):
     if args.impl == "reference":
         run_reference(args)
     else:

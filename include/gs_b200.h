@@ -103,7 +103,9 @@ int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *p
  * 64-bit keys (ties in emission order), at a third of the memory traffic.
  *
  * gs_sort_points_by_depth: order [m] i32 = row indices of the visible list sorted by depth_key
- *   (stable; depth_key >= 0 must fit `depth_bits` <= 31 bits).
+ *   (stable; depth_key >= 0 must fit `depth_bits` <= 31 bits).  If m_dev is not null, m is only a
+ *   capacity (buffers and workspace sized for it) and the count is read on the device from *m_dev
+ *   -- the host can enqueue the sort before it has read the totals of gs_project_cull_sh back.
  * gs_emit_tile_keys: walks `order`, and for every tile of every point's bounding box writes
  *   tile_ids [k] u32 and payload [k] i32 (= row index), contiguous per point, points in `order`.
  * gs_sort_pairs32: stable ascending sort of (u32 key, i32 payload) by the low `key_bits` bits;
@@ -112,8 +114,8 @@ int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *p
  * gs_sorted_keys: rebuilds the reference's sorted 64-bit keys (depth_key[payload] + (tile << 32),
  *   R.py:159-160) for inspection and the parity tests; not on the product path.
  */
-int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int depth_bits, int32_t *order,
-                            void *workspace, void *stream);
+int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, const int64_t *m_dev, int depth_bits,
+                            int32_t *order, void *workspace, void *stream);
 int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k, int width,
                       uint32_t *tile_ids, int32_t *payload, void *workspace, void *stream);
 int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_alt, int32_t *payload_alt,

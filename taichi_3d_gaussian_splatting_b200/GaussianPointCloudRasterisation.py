@@ -341,10 +341,23 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         buf.ptr("tile_offsets"), buf.ptr("records"), buf.ptr("bbox"), buf.ptr("depth_key"),
         totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
     _mark("project_cull_sh")
+    num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
+    depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
+                                          float(cfg.depth_to_sort_key_scale), num_tiles)
+    depth_first = KEY_PIPELINE == "depth_first" and depth_bits <= 31
+    order = None
+    if depth_first and n > 0:
+        # The argsort of the visible points by depth needs M only on the device: enqueue it for
+        # capacity N now, so the GPU works while the host waits for {M, K} below.
+        order = torch.empty(n, dtype=torch.int32, device=dev)
+        pts_ws = torch.empty(int(_lib.gs_point_sort_workspace_bytes(n)), dtype=torch.uint8, device=dev)
+        _capi.check(_lib.gs_sort_points_by_depth(buf.ptr("depth_key"), n, totals.data_ptr(), depth_bits,
+                                                 order.data_ptr(), pts_ws.data_ptr(), stream),
+                    "gs_sort_points_by_depth")
+        _mark("sort_points")
     m, k = (int(v) for v in totals.tolist())  # the one host sync of the forward
     st.m, st.k = m, k
 
-    num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
     st.tile_start = torch.empty(num_tiles, dtype=torch.int32, device=dev)
     st.tile_end = torch.empty(num_tiles, dtype=torch.int32, device=dev)
     st.image = torch.empty(H, W, 3, dtype=torch.float32, device=dev)
@@ -361,26 +374,17 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         st.last = torch.empty(H, W, dtype=torch.int32, device=dev)
         st.count = torch.empty(H, W, dtype=torch.int32, device=dev)
 
-    depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
-                                          float(cfg.depth_to_sort_key_scale), num_tiles)
-    depth_first = KEY_PIPELINE == "depth_first" and depth_bits <= 31
     kk = max(k, 1)
     st.tile_ids = None
     if depth_first:
         # points sorted by depth -> tile ids emitted in that order -> stable sort by tile id only
         tid2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
         pay2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
-        order = torch.empty(max(m, 1), dtype=torch.int32, device=dev)
-        ws_bytes = max(int(_lib.gs_point_sort_workspace_bytes(m)), int(_lib.gs_sort_workspace_bytes(k)),
-                       int(_lib.gs_emit_workspace_bytes(m)), 16)
+        ws_bytes = max(int(_lib.gs_sort_workspace_bytes(k)), int(_lib.gs_emit_workspace_bytes(m)), 16)
         sort_ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
         _mark("host_sync_and_alloc")
         st.keys = None
         if k > 0:
-            _capi.check(_lib.gs_sort_points_by_depth(buf.ptr("depth_key"), m, depth_bits,
-                                                     order.data_ptr(), sort_ws.data_ptr(), stream),
-                        "gs_sort_points_by_depth")
-            _mark("sort_points")
             _capi.check(_lib.gs_emit_tile_keys(order.data_ptr(), buf.ptr("bbox"), m, k, W,
                                                tid2.data_ptr(), pay2.data_ptr(), sort_ws.data_ptr(),
                                                stream), "gs_emit_tile_keys")

@@ -171,7 +171,7 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             for (int j = 0; j < kCells; ++j) live |= (my_i < cell_last[j] ? 1u : 0u) << j;
             if (live)
                 my_mask = live & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z,
-                                                      x_first, y_first);
+                                                      x_first, y_first);  // (drops the irregular flag)
         }
         s_rec[3 * lane] = n0;
         s_rec[3 * lane + 1] = n1;

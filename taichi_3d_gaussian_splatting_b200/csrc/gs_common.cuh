@@ -97,8 +97,11 @@ __device__ __forceinline__ void gs_sh_basis(float dx, float dy, float dz, float 
 // 2 ln(255 * peak), peak = rescale * opacity, there; per pixel row the minimum over the row's 8
 // centres is taken at dx clamped to the row, so the test is exact up to the margin (0.05 absolute
 // + 4e-6 relative to the positive terms, far above the rounding of either arithmetic profile).
-// Conics that are not positive definite / finite keep every bit.
+// Conics that are not positive definite / finite keep every bit (plus kCellMaskIrregular).
 constexpr int kCellW = 8, kCellH = 4;
+// set together with every cell bit for a conic that is not positive definite / finite: only such
+// an entry can produce an exponent above zero or NaN, so only it needs the guarded exp
+constexpr unsigned kCellMaskIrregular = 1u << 8;
 
 template <int kCells>
 __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, float b, float c,
@@ -106,7 +109,7 @@ __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, floa
 {
     constexpr unsigned kAll = (1u << kCells) - 1u;
     if (!(a > 0.0f) || !(c > 0.0f) || !(a * c > b * b) || !isfinite(a + b + c + u + v + peak))
-        return kAll;
+        return kAll | kCellMaskIrregular;
     if (!(peak * 255.0f >= 0.97f)) return 0u;  // alpha <= peak < 1/255 everywhere (e <= 0)
     const float tau = fmaf(2.0f, __logf(peak * 255.0f), 0.05f);
     const float slope = -b / a;  // unconstrained minimiser of a row: dx = slope * dy

@@ -47,9 +47,10 @@ __device__ __forceinline__ unsigned int compact_key(unsigned int key, const KeyS
 
 template <typename KeyT>
 __global__ void __launch_bounds__(256)
-histogram_kernel(const KeyT *__restrict__ keys, long long k, KeySpec spec, int num_passes,
-                 uint32_t *__restrict__ ghist)
+histogram_kernel(const KeyT *__restrict__ keys, long long k, const long long *__restrict__ k_dev,
+                 KeySpec spec, int num_passes, uint32_t *__restrict__ ghist)
 {
+    if (k_dev) k = *k_dev;  // the count lives on the device; the host only knows a capacity
     __shared__ uint32_t sh[kMaxPasses * kRadix];
     for (int i = threadIdx.x; i < num_passes * kRadix; i += blockDim.x) sh[i] = 0;
     __syncthreads();
@@ -92,9 +93,11 @@ template <typename KeyT, bool kBallot>
 __global__ void __launch_bounds__(kSortBlock, sizeof(KeyT) == 4 ? 3 : 2)
 onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ vals_in,
                 KeyT *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
-                KeySpec spec, int shift, int digit_bits, const uint32_t *__restrict__ gbase,
-                uint32_t *__restrict__ status, unsigned int *__restrict__ ticket)
+                const long long *__restrict__ k_dev, KeySpec spec, int shift, int digit_bits,
+                const uint32_t *__restrict__ gbase, uint32_t *__restrict__ status,
+                unsigned int *__restrict__ ticket)
 {
+    if (k_dev) k = *k_dev;  // launched for a capacity: tiles past the real count leave at once
     extern __shared__ __align__(16) unsigned char smem[];
     KeyT *s_keys = reinterpret_cast<KeyT *>(smem);
     int32_t *s_vals = reinterpret_cast<int32_t *>(s_keys + kSortTile);
@@ -111,6 +114,7 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
     __syncthreads();
     const long long tile = s_ticket;
     const long long tile_base = tile * kSortTile;
+    if (tile_base >= k) return;
     const int valid = (int)min((long long)kSortTile, k - tile_base);
 
     KeyT key[kItems];
@@ -301,7 +305,7 @@ inline int64_t sort_tiles(int64_t k) { return (k + kSortTile - 1) / kSortTile; }
 template <typename KeyT>
 int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, int32_t *vals_a,
               KeyT *keys_b, int32_t *vals_b, int64_t k, const KeySpec &spec, int total_bits,
-              void *workspace, cudaStream_t st)
+              void *workspace, cudaStream_t st, const long long *k_dev = nullptr)
 {
     const int num_passes = (total_bits + 7) / 8;
     const int64_t tiles = sort_tiles(k);
@@ -328,7 +332,7 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
 
     int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
     if (hist_blocks < 1) hist_blocks = 1;
-    histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, spec, num_passes, ghist);
+    histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, k_dev, spec, num_passes, ghist);
     GS_LAUNCH_CHECK();
     scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ghist, gbase);
     GS_LAUNCH_CHECK();
@@ -341,11 +345,11 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
         const int digit_bits = min(8, total_bits - 8 * p);
         if (ballot)
             onesweep_kernel<KeyT, true><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
-                kin, vin, kout, vout, k, spec, 8 * p, digit_bits, gbase + p * kRadix,
+                kin, vin, kout, vout, k, k_dev, spec, 8 * p, digit_bits, gbase + p * kRadix,
                 status + (size_t)p * tiles * kRadix, tickets + p);
         else
             onesweep_kernel<KeyT, false><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
-                kin, vin, kout, vout, k, spec, 8 * p, digit_bits, gbase + p * kRadix,
+                kin, vin, kout, vout, k, k_dev, spec, 8 * p, digit_bits, gbase + p * kRadix,
                 status + (size_t)p * tiles * kRadix, tickets + p);
         GS_LAUNCH_CHECK();
         kin = kout;
@@ -416,8 +420,8 @@ extern "C" int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_
     return GS_OK;
 }
 
-extern "C" int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int depth_bits,
-                                       int32_t *order, void *workspace, void *stream)
+extern "C" int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, const int64_t *m_dev,
+                                       int depth_bits, int32_t *order, void *workspace, void *stream)
 {
     if (m < 0 || depth_bits < 1 || depth_bits > 31) return GS_E_INVALID;
     if (m >= (1ll << 30)) return GS_E_CAPACITY;
@@ -434,5 +438,6 @@ extern "C" int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, int 
     int32_t *vals_a = (num_passes & 1) ? order : vals_tmp;
     int32_t *vals_b = (num_passes & 1) ? vals_tmp : order;
     return sort_impl<unsigned int>((const unsigned int *)depth_key, nullptr, keys_a, vals_a, keys_b,
-                                   vals_b, m, spec, depth_bits, workspace, (cudaStream_t)stream);
+                                   vals_b, m, spec, depth_bits, workspace, (cudaStream_t)stream,
+                                   (const long long *)m_dev);
 }

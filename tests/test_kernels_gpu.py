@@ -96,12 +96,24 @@ def test_sort_points_by_depth_is_a_stable_argsort(m, bits):
     d = torch.from_numpy(depth).to(dev)
     order = torch.empty(m, dtype=torch.int32, device=dev)
     ws = torch.empty(int(capi.lib.gs_point_sort_workspace_bytes(m)), dtype=torch.uint8, device=dev)
-    capi.check(capi.lib.gs_sort_points_by_depth(d.data_ptr(), m, bits, order.data_ptr(), ws.data_ptr(),
+    capi.check(capi.lib.gs_sort_points_by_depth(d.data_ptr(), m, None, bits, order.data_ptr(), ws.data_ptr(),
                                                 torch.cuda.current_stream().cuda_stream),
                "gs_sort_points_by_depth")
     torch.cuda.synchronize()
     assert np.array_equal(d.cpu().numpy(), depth)  # input untouched
-    assert np.array_equal(order.cpu().numpy(), np.argsort(depth, kind="stable").astype(np.int32))
+    want = np.argsort(depth, kind="stable").astype(np.int32)
+    assert np.array_equal(order.cpu().numpy(), want)
+    # capacity form: the count is read on the device, buffers sized for a larger capacity
+    cap = m + 5000
+    d2 = torch.cat([d, torch.full((cap - m,), 7, dtype=torch.int32, device=dev)])
+    order2 = torch.full((cap,), -1, dtype=torch.int32, device=dev)
+    ws2 = torch.empty(int(capi.lib.gs_point_sort_workspace_bytes(cap)), dtype=torch.uint8, device=dev)
+    count = torch.tensor([m, 0], dtype=torch.int64, device=dev)
+    capi.check(capi.lib.gs_sort_points_by_depth(d2.data_ptr(), cap, count.data_ptr(), bits, order2.data_ptr(),
+                                                ws2.data_ptr(), torch.cuda.current_stream().cuda_stream),
+               "gs_sort_points_by_depth")
+    torch.cuda.synchronize()
+    assert np.array_equal(order2[:m].cpu().numpy(), want)
 
 
 def test_emit_tile_keys_follows_the_given_order():
