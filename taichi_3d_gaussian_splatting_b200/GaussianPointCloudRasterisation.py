@@ -259,6 +259,27 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
         )
 
 
+_READBACK: Dict[int, tuple] = {}  # device index -> (side stream, pinned int64[2])
+
+
+def _read_totals(totals: torch.Tensor, ready: "torch.cuda.Event"):
+    """{M, K} to the host without waiting for work enqueued after `ready` (the point sort): the
+    copy runs on a side stream that waits only for the projection kernel."""
+    dev = totals.device
+    key = dev.index if dev.index is not None else torch.cuda.current_device()
+    if key not in _READBACK:
+        _READBACK[key] = (torch.cuda.Stream(dev), torch.empty(2, dtype=torch.int64).pin_memory())
+    side, host = _READBACK[key]
+    with torch.cuda.stream(side):
+        side.wait_event(ready)
+        host.copy_(totals, non_blocking=True)
+        done = torch.cuda.Event()
+        done.record(side)
+    totals.record_stream(side)
+    done.synchronize()
+    return int(host[0]), int(host[1])
+
+
 class _ForwardState:
     """Everything the backward needs, plus handles a test can read every stage from."""
     __slots__ = ("n", "m", "k", "width", "height", "buffers", "payload", "keys", "tile_start",
@@ -341,6 +362,8 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         buf.ptr("tile_offsets"), buf.ptr("records"), buf.ptr("bbox"), buf.ptr("depth_key"),
         totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
     _mark("project_cull_sh")
+    after_project = torch.cuda.Event()
+    after_project.record(torch.cuda.current_stream(dev))
     num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
     depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
                                           float(cfg.depth_to_sort_key_scale), num_tiles)
@@ -355,9 +378,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                                                  order.data_ptr(), pts_ws.data_ptr(), stream),
                     "gs_sort_points_by_depth")
         _mark("sort_points")
-    m, k = (int(v) for v in totals.tolist())  # the one host sync of the forward
-    st.m, st.k = m, k
-
+    # everything that does not depend on {M, K} is allocated while the GPU is still busy
     st.tile_start = torch.empty(num_tiles, dtype=torch.int32, device=dev)
     st.tile_end = torch.empty(num_tiles, dtype=torch.int32, device=dev)
     st.image = torch.empty(H, W, 3, dtype=torch.float32, device=dev)
@@ -373,6 +394,9 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         st.acc_alpha = torch.empty(H, W, dtype=torch.float32, device=dev)
         st.last = torch.empty(H, W, dtype=torch.int32, device=dev)
         st.count = torch.empty(H, W, dtype=torch.int32, device=dev)
+
+    m, k = _read_totals(totals, after_project)  # the one host sync of the forward
+    st.m, st.k = m, k
 
     kk = max(k, 1)
     st.tile_ids = None
