@@ -55,7 +55,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     procs = []
     for unit, extra in UNITS.items():
         obj = os.path.join(objdir, unit.replace(".cu", ".o"))
-        cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", os.path.join(CSRC, unit), "-o", obj]
+        tune = os.environ.get("GS_EXTRA_NVCC_FLAGS", "").split()  # tuning experiments only
+        cmd = [nvcc, *ARCH, *COMMON, *extra, *tune, "-c", os.path.join(CSRC, unit), "-o", obj]
         if verbose:
             cmd.insert(1, "-Xptxas=-v")
             print(" ".join(cmd), flush=True)

@@ -92,7 +92,7 @@ __device__ __forceinline__ void gs_sh_basis(float dx, float dy, float dz, float 
 
 // ---- per-cell culling shared by the two blend kernels --------------------------------------------
 // A warp owns a column of kCells cells of 8x4 pixels.  Bit j of the result is set <=> the splat
-// may reach alpha >= 1/255 at a pixel centre of cell j (rows [4j, 4j+4) of the column, first
+// may reach alpha >= 1/255 at a pixel centre of cell j (rows [kRows j, kRows (j+1)) of the column, first
 // pixel centre (x_first, y_first)).  q(d) = a dx^2 + 2 b dx dy + c dy^2 must stay <= tau =
 // 2 ln(255 * peak), peak = rescale * opacity, there; per pixel row the minimum over the row's 8
 // centres is taken at dx clamped to the row, so the test is exact up to the margin (0.05 absolute
@@ -103,7 +103,7 @@ constexpr int kCellW = 8, kCellH = 4;
 // an entry can produce an exponent above zero or NaN, so only it needs the guarded exp
 constexpr unsigned kCellMaskIrregular = 1u << 8;
 
-template <int kCells>
+template <int kCells, int kRows = kCellH>
 __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, float b, float c,
                                                  float peak, float x_first, float y_first)
 {
@@ -117,12 +117,12 @@ __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, floa
     const float b2 = 2.0f * b;
     unsigned mask = 0u;
 #pragma unroll
-    for (int r = 0; r < kCells * kCellH; ++r) {
+    for (int r = 0; r < kCells * kRows; ++r) {
         const float dy = (y_first + (float)r) - v;
         const float dx = fminf(fmaxf(slope * dy, lo), hi);
         const float pos = fmaf(a * dx, dx, (c * dy) * dy);
         const float q = fmaf(b2 * dx, dy, pos);
-        if (q <= fmaf(4e-6f, pos, tau)) mask |= 1u << (r / kCellH);
+        if (q <= fmaf(4e-6f, pos, tau)) mask |= 1u << (r / kRows);
     }
     return mask;
 }
