@@ -175,6 +175,54 @@ int gs_point_bwd(const float *xyz, const float *features, const int32_t *object_
                  float *hook_grad_xyz, float *hook_grad_features, float *hook_grad_viewspace,
                  float *hook_magnitude, int32_t *hook_num_affected, int accumulate, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * Loss front-end: what runs between the rasteriser's image and the
+ * cotangent handed back to gs_blend_bwd.  Replaces, per iteration, GaussianPointTrainer.py:172-182
+ * (`torch.clamp(image, 0, 1)`, `permute(2, 0, 1)`, `loss.backward()`) and LossFunction.py:20-52
+ * (`L = (1 - lambda) L1 + lambda (1 - ssim(...))`, scale regulariser), including
+ * pytorch_msssim.ssim(X, Y, data_range=1, size_average=True): 11-tap window, sigma 1.5, valid
+ * filtering, K1 = 0.01, K2 = 0.03.
+ *
+ * `image` and `gt` are 3-channel fp32 images addressed by element strides (h, w, c), so both the
+ * rasteriser's H x W x 3 output and a permuted 3 x H x W view are read in place.  The clamp to
+ * [0, 1] is applied on load (a no-op for an image that is already clamped).  H, W >= 11.
+ * --------------------------------------------------------------------------------------------- */
+int64_t gs_loss_workspace_bytes(int height, int width); /* `workspace` of gs_loss_fwd */
+int64_t gs_loss_maps_bytes(int height, int width);      /* `maps`: 9 (H-10)(W-10) floats */
+
+/*
+ * Forward.  scalars [6] f32 receives
+ *   0: L   1: L1   2: 1 - SSIM   3: regulariser value (0 if absent)   4: valid points   5: SSIM
+ * (LossFunction.forward returns (0, 1, 2)).  `maps` receives the three SSIM derivative maps
+ * gs_loss_bwd consumes.  With features != null the scale regulariser (LossFunction.py:40-52:
+ * mean over points with invalid_mask == 0 of ||exp(features[:, 4:7])||_2) times reg_weight is
+ * added to L; features is [n, 56] f32, invalid_mask [n] i8.
+ */
+int gs_loss_fwd(const float *image, int64_t image_stride_h, int64_t image_stride_w,
+                int64_t image_stride_c, const float *gt, int64_t gt_stride_h, int64_t gt_stride_w,
+                int64_t gt_stride_c, int height, int width, float lambda_value,
+                const float *features, const int8_t *invalid_mask, int64_t n, float reg_weight,
+                float *maps, void *workspace, float *scalars, void *stream);
+
+/*
+ * Backward of the image terms: grad_image [H, W, 3] f32 (contiguous, the rasteriser's layout)
+ * receives upstream * dL/d(image), zero where the clamp is active.  `upstream` is a device scalar
+ * (the cotangent of L) or null for 1.
+ */
+int gs_loss_bwd(const float *image, int64_t image_stride_h, int64_t image_stride_w,
+                int64_t image_stride_c, const float *gt, int64_t gt_stride_h, int64_t gt_stride_w,
+                int64_t gt_stride_c, int height, int width, float lambda_value, const float *maps,
+                const float *upstream, float *grad_image, void *stream);
+
+/*
+ * Backward of the scale regulariser into columns 4:7 of grad_features [n, 56] (stored, or added
+ * with accumulate != 0; other columns are not touched).  `scalars` is gs_loss_fwd's output (slot
+ * 4 is read).
+ */
+int gs_scale_reg_bwd(const float *features, const int8_t *invalid_mask, int64_t n, float reg_weight,
+                     const float *scalars, const float *upstream, float *grad_features,
+                     int accumulate, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
 
-ABI_VERSION = 103
+ABI_VERSION = 104
 
 _p = C.c_void_p
 _i = C.c_int
@@ -44,6 +44,11 @@ SIGNATURES = {
     "gs_blend_bwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "gs_point_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p, _p, _i, _f, _f, _f, _f, _f,
                           _p, _p, _p, _p, _p, _p, _p, _i, _p]),
+    "gs_loss_workspace_bytes": (_l, [_i, _i]),
+    "gs_loss_maps_bytes": (_l, [_i, _i]),
+    "gs_loss_fwd": (_i, [_p, _l, _l, _l, _p, _l, _l, _l, _i, _i, _f, _p, _p, _l, _f, _p, _p, _p, _p]),
+    "gs_loss_bwd": (_i, [_p, _l, _l, _l, _p, _l, _l, _l, _i, _i, _f, _p, _p, _p, _p]),
+    "gs_scale_reg_bwd": (_i, [_p, _p, _l, _f, _p, _p, _p, _i, _p]),
 }
 
 

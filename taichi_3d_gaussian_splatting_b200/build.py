@@ -3,7 +3,7 @@
 Two arithmetic profiles, chosen per translation unit ("Arithmetic profiles"):
   literal fp32  -- project.cu, blend_fwd.cu: -fmad=false, so only explicit fmaf() fuses and the
                    results are bit-exact with oracle/gs_oracle.c
-  fast fp32     -- blend_bwd.cu, point_bwd.cu (and the integer kernels): default contraction
+  fast fp32     -- blend_bwd.cu, point_bwd.cu, loss.cu (and the integer kernels): default contraction
 """
 from __future__ import annotations
 
@@ -27,6 +27,7 @@ UNITS = {
     "blend_fwd.cu": ["-fmad=false"],
     "blend_bwd.cu": [],
     "point_bwd.cu": [],
+    "loss.cu": [],
 }
 
 
