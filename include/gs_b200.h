@@ -223,6 +223,39 @@ int gs_scale_reg_bwd(const float *features, const int8_t *invalid_mask, int64_t 
                      const float *scalars, const float *upstream, float *grad_features,
                      int accumulate, void *stream);
 
+/* ---------------------------------------------------------------------------------------------
+ * After the backward.
+ * --------------------------------------------------------------------------------------------- */
+
+/*
+ * Densification statistics.  Replaces the body of GaussianPointAdaptiveController.update
+ * (GaussianPointAdaptiveController.py:130-146): for each of the m visible points (hook payload, list
+ * order; ids distinct) with id = ids[i]
+ *   acc_num_in_camera[id] += 1;  acc_num_pixels[id] += num_affected[i];
+ *   acc_view_grad[id] += magnitude[i];
+ *   acc_view_grad_avg[id] += magnitude[i] / num_affected[i]   (NaN counted as 0);
+ *   acc_pos_grad[id, 0:3] += grad_xyz[i, 0:3];  acc_pos_grad_norm[id] += ||grad_xyz[i]||_2.
+ * The accumulators are the controller's [n] / [n,3] tensors (AC.py:113-125).
+ */
+int gs_controller_accumulate(const int32_t *ids, int64_t m, const int32_t *num_affected,
+                             const float *magnitude, const float *grad_xyz,
+                             int32_t *acc_num_in_camera, int32_t *acc_num_pixels,
+                             float *acc_view_grad, float *acc_view_grad_avg, float *acc_pos_grad,
+                             float *acc_pos_grad_norm, void *stream);
+
+/*
+ * One Adam update of `count` fp32 elements, in place.  Replaces torch.optim.Adam.step for the
+ * trainer's two optimisers (GaussianPointTrainer.py:131-134,183-184; amsgrad off, no weight decay):
+ *   m += (1 - beta1) (g - m);  v = beta2 v + (1 - beta2) g^2;
+ *   p -= lr / (1 - beta1^step) * m / (sqrt(v) / sqrt(1 - beta2^step) + eps).
+ * `step` is the 1-based update count.  `grad` is read in place (e.g. a slice of the all-reduced
+ * N x 59 gradient buffer).  row_mask (nullable): [count / row_len] i8; elements of rows whose
+ * byte is non-zero are left untouched (not reference behaviour; null = update everything).
+ */
+int gs_adam_step(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t count,
+                 float lr, float beta1, float beta2, float eps, int64_t step, const int8_t *row_mask,
+                 int row_len, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
 
-ABI_VERSION = 104
+ABI_VERSION = 105
 
 _p = C.c_void_p
 _i = C.c_int
@@ -49,6 +49,8 @@ SIGNATURES = {
     "gs_loss_fwd": (_i, [_p, _l, _l, _l, _p, _l, _l, _l, _i, _i, _f, _p, _p, _l, _f, _p, _p, _p, _p]),
     "gs_loss_bwd": (_i, [_p, _l, _l, _l, _p, _l, _l, _l, _i, _i, _f, _p, _p, _p, _p]),
     "gs_scale_reg_bwd": (_i, [_p, _p, _l, _f, _p, _p, _p, _i, _p]),
+    "gs_controller_accumulate": (_i, [_p, _l, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "gs_adam_step": (_i, [_p, _p, _p, _p, _l, _f, _f, _f, _f, _l, _p, _i, _p]),
 }
 
 

@@ -28,6 +28,7 @@ UNITS = {
     "blend_bwd.cu": [],
     "point_bwd.cu": [],
     "loss.cu": [],
+    "train_ops.cu": [],
 }
 
 
