@@ -43,29 +43,49 @@ __device__ __forceinline__ float warp_sum(float v)
     return v;
 }
 
-// Loads the 42x42 halo of all three channels into s[c][row][kInStride]; positions outside the
-// image read as 0.  The fastest-running index follows the tensor's unit stride (HWC or CHW).
-template <bool kClamp>
-__device__ __forceinline__ void load_halo(float *s, const float *src, const Strides st, const int y0,
-                                          const int x0, const int height, const int width)
+// 4-byte asynchronous global -> shared copy (LDGSTS); !valid writes a zero without reading.
+__device__ __forceinline__ void cp_async4(float *dst, const float *src, const bool valid)
 {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    const int bytes = valid ? 4 : 0;
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all()
+{
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
+}
+
+// Starts the copy of the 42x42 halo of all three channels into s[c][row][kInStride]; positions
+// outside the image become 0.  One warp per row; the lanes run along the tensor's unit stride
+// (channel-interleaved HWC rows of 126 floats, or planar rows of 42).  No register staging: every
+// copy of the block is in flight at once (cp_async_wait_all + __syncthreads before use).
+__device__ __forceinline__ void load_halo_async(float *s, const float *src, const Strides st, const int y0,
+                                                const int x0, const int height, const int width)
+{
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (st.c == 1) {
-        for (int i = threadIdx.x; i < kHalo * kHalo * 3; i += kLossThreads) {
-            const int r = i / (kHalo * 3), j = i - r * (kHalo * 3);
-            const int col = j / 3, ch = j - col * 3;
-            const int y = y0 + r, x = x0 + col;
-            float v = 0.0f;
-            if (y >= 0 && y < height && x >= 0 && x < width) v = src[y * st.h + x * st.w + ch];
-            s[(ch * kHalo + r) * kInStride + col] = kClamp ? clamp01(v) : v;
+        for (int r = warp; r < kHalo; r += kLossThreads / 32) {
+            const int y = y0 + r;
+            const bool row_ok = y < height;
+            const float *row = src + (row_ok ? y * st.h : 0);
+#pragma unroll
+            for (int j = lane; j < 3 * kHalo; j += 32) {
+                const int col = j / 3, ch = j - col * 3;
+                const bool ok = row_ok && (x0 + col) < width;
+                cp_async4(s + (ch * kHalo + r) * kInStride + col, ok ? row + (x0 + col) * st.w + ch : src, ok);
+            }
         }
     } else {
-        for (int i = threadIdx.x; i < kHalo * kHalo * 3; i += kLossThreads) {
-            const int cr = i / kHalo, col = i - cr * kHalo;
+        for (int cr = warp; cr < 3 * kHalo; cr += kLossThreads / 32) {
             const int ch = cr / kHalo, r = cr - ch * kHalo;
-            const int y = y0 + r, x = x0 + col;
-            float v = 0.0f;
-            if (y >= 0 && y < height && x >= 0 && x < width) v = src[y * st.h + x * st.w + ch * st.c];
-            s[(ch * kHalo + r) * kInStride + col] = kClamp ? clamp01(v) : v;
+            const int y = y0 + r;
+            const bool row_ok = y < height;
+            const float *row = src + (row_ok ? y * st.h + ch * st.c : 0);
+#pragma unroll
+            for (int col = lane; col < kHalo; col += 32) {
+                const bool ok = row_ok && (x0 + col) < width;
+                cp_async4(s + cr * kInStride + col, ok ? row + (x0 + col) * st.w : src, ok);
+            }
         }
     }
 }
@@ -101,23 +121,28 @@ loss_fwd_kernel(const float *__restrict__ image, const Strides ist, const float 
 
     const int oh = height - (kWin - 1), ow = width - (kWin - 1);
     const int y0 = blockIdx.y * kLossTile, x0 = blockIdx.x * kLossTile;
-    load_halo<true>(sx, image, ist, y0, x0, height, width);
-    load_halo<false>(sy, gt, gst, y0, x0, height, width);
+    load_halo_async(sx, image, ist, y0, x0, height, width);
+    load_halo_async(sy, gt, gst, y0, x0, height, width);
+    cp_async_wait_all();
     __syncthreads();
 
-    // L1 over the pixels this block owns: its 32x32 input square, the last row / column of blocks
-    // also taking what is left of the image (at most 10 more rows / columns, inside the halo).
+    // One pass over the halo: clamp the prediction in place (GaussianPointTrainer.py:173) and sum
+    // |x - y| over the pixels this block owns: its 32x32 input square, the last row / column of
+    // blocks also taking what is left of the image (at most 10 more rows / columns, inside the halo).
     float l1 = 0.0f;
     {
         const int own_h = (blockIdx.y == gridDim.y - 1) ? min(kHalo, height - y0) : kLossTile;
         const int own_w = (blockIdx.x == gridDim.x - 1) ? min(kHalo, width - x0) : kLossTile;
-        for (int i = threadIdx.x; i < 3 * own_h * own_w; i += kLossThreads) {
-            const int cr = i / own_w, col = i - cr * own_w;
-            const int ch = cr / own_h, r = cr - ch * own_h;
-            const int o = (ch * kHalo + r) * kInStride + col;
-            l1 += fabsf(sx[o] - sy[o]);
+        for (int i = threadIdx.x; i < 3 * kHalo * kInStride; i += kLossThreads) {
+            const int cr = i / kInStride, col = i - cr * kInStride;
+            const int r = cr % kHalo;
+            if (col >= kHalo) continue;  // padding column
+            const float x = clamp01(sx[i]);
+            sx[i] = x;
+            if (r < own_h && col < own_w) l1 += fabsf(x - sy[i]);
         }
     }
+    __syncthreads();
 
     float w[kWin];
 #pragma unroll
@@ -320,15 +345,21 @@ loss_bwd_kernel(const float *__restrict__ image, const Strides ist, const float 
 
     const int vc = threadIdx.x & 31, vg = threadIdx.x >> 5;
     for (int ch = 0; ch < 3; ++ch) {
-        // halo of the three maps: map positions (y0-10 .. y0+31, x0-10 .. x0+31), zero outside
-        for (int i = threadIdx.x; i < 3 * kHalo * kHalo; i += kLossThreads) {
-            const int qr = i / kHalo, col = i - qr * kHalo;
+        // halo of the three maps: map positions (y0-10 .. y0+31, x0-10 .. x0+31), zero outside;
+        // one warp per row, all copies in flight at once
+        for (int qr = threadIdx.x >> 5; qr < 3 * kHalo; qr += kLossThreads / 32) {
             const int q = qr / kHalo, r = qr - q * kHalo;
-            const int my = y0 - (kWin - 1) + r, mx = x0 - (kWin - 1) + col;
-            float v = 0.0f;
-            if (my >= 0 && my < oh && mx >= 0 && mx < ow) v = maps[(q * 3 + ch) * plane + (size_t)my * ow + mx];
-            sin[(q * kHalo + r) * kInStride + col] = v;
+            const int my = y0 - (kWin - 1) + r;
+            const bool row_ok = my >= 0 && my < oh;
+            const float *row = maps + (q * 3 + ch) * plane + (row_ok ? (size_t)my * ow : 0);
+#pragma unroll
+            for (int col = threadIdx.x & 31; col < kHalo; col += 32) {
+                const int mx = x0 - (kWin - 1) + col;
+                const bool ok = row_ok && mx >= 0 && mx < ow;
+                cp_async4(sin + qr * kInStride + col, ok ? row + mx : maps, ok);
+            }
         }
+        cp_async_wait_all();
         __syncthreads();
         // horizontal: out(x) = sum_k w[k] * m(x - k); halo column of m(x - k) is (x - x0) + 10 - k
         for (int task = threadIdx.x; task < kHalo * (kLossTile / 4); task += kLossThreads) {
@@ -388,9 +419,9 @@ loss_bwd_kernel(const float *__restrict__ image, const Strides ist, const float 
     }
     // coalesced store of the tile: rows of up to 96 consecutive floats of the HWC gradient
     const int tw = min(kLossTile, width - x0), th = min(kLossTile, height - y0);
-    for (int i = threadIdx.x; i < th * 3 * tw; i += kLossThreads) {
-        const int r = i / (3 * tw), j = i - r * (3 * tw);
-        grad_image[((size_t)(y0 + r) * width + x0) * 3 + j] = sout[r * (3 * kLossTile + 1) + j];
+    for (int r = threadIdx.x >> 5; r < th; r += kLossThreads / 32) {
+        float *row = grad_image + ((size_t)(y0 + r) * width + x0) * 3;
+        for (int j = threadIdx.x & 31; j < 3 * tw; j += 32) row[j] = sout[r * (3 * kLossTile + 1) + j];
     }
 }
 
