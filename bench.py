@@ -422,6 +422,13 @@ def run_b200(args):
                     "unit": "GB/s", "frac": round(d["gb_s"] / hbm_peak, 4), "traffic": None,
                     "peak_source": peak_src, "ms_per_launch": d["ms"],
                     "algorithmic_bytes": d["algorithmic_bytes"]}
+        try:  # measured DRAM bytes per launch of that kernel, from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")) as f:
+                entry = json.load(f).get(args.workload, {}).get(dominant)
+            if entry:
+                roofline.update(traffic=entry["bytes"], traffic_source=entry["source"])
+        except (OSError, ValueError):
+            pass
         if "fp32_tflops" in d:  # the blend kernels are FP32-issue bound, not HBM bound
             roofline.update(alt_bound="fp32", alt_achieved=d["fp32_tflops"],
                             alt_peak=round(FP32_PEAK_TFLOPS, 1), alt_unit="TFLOP/s",
