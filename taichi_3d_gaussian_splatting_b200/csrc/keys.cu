@@ -92,6 +92,7 @@ __global__ void tile_ranges_kernel(const long long *__restrict__ keys, long long
 // point order: the order a stable sort of the reference's 64-bit keys produces.
 constexpr unsigned long long kEmitAggregate = 1ull << 62;
 constexpr unsigned long long kEmitPrefix = 2ull << 62;
+constexpr int kEmitChunk = 2048;  // slots per owner scan: 8 per thread
 constexpr unsigned long long kEmitValueMask = (1ull << 62) - 1;
 
 __global__ void __launch_bounds__(kEmitBlock)
@@ -100,7 +101,10 @@ emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restri
                       int32_t *__restrict__ payload, unsigned long long *__restrict__ status,
                       unsigned int *__restrict__ ticket)
 {
-    __shared__ unsigned int s_end[kEmitBlock];
+    __shared__ unsigned int s_start[kEmitBlock];
+    __shared__ float s_rcp[kEmitBlock];
+    __shared__ __align__(16) int s_owner[kEmitChunk];
+    __shared__ int s_warp_max[kEmitBlock / 32];
     __shared__ ushort4 s_box[kEmitBlock];
     __shared__ int32_t s_row[kEmitBlock];
     __shared__ unsigned int s_warp_total[kEmitBlock / 32];
@@ -140,7 +144,8 @@ emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restri
     }
     s_box[tid] = box;
     s_row[tid] = row;
-    s_end[tid] = warp_excl + incl;
+    s_start[tid] = warp_excl + incl - cnt;
+    s_rcp[tid] = 1.0f / (float)max((int)box.w - (int)box.z, 1);
     if (warp == 0) {
         if (lane == 0)
             gs_st_volatile_u64(status + block, (block == 0 ? kEmitPrefix : kEmitAggregate) | block_total);
@@ -169,23 +174,80 @@ emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restri
     __syncthreads();
     const unsigned long long base = s_base;
     const unsigned int total = block_total;
-    for (unsigned int s = tid; s < total; s += kEmitBlock) {
-        int lo = 0, hi = npts - 1;
-        while (lo < hi) {
-            int mid = (lo + hi) >> 1;
-            if (s_end[mid] > s) hi = mid; else lo = mid + 1;
+    // Owner of every slot by a max-scan instead of a search per slot: in chunks of kEmitChunk slots,
+    // each entry marks the slot its run starts at, an inclusive max-scan spreads the mark over the
+    // run (8 consecutive slots per thread, then warp and block level), and the threads then walk the
+    // chunk with stride kEmitBlock so that the stores are coalesced.
+    const unsigned int my_start = warp_excl + incl - cnt;
+    int4 *s_owner4 = reinterpret_cast<int4 *>(s_owner);
+    for (unsigned int cb = 0; cb < total; cb += kEmitChunk) {
+        s_owner4[2 * tid] = make_int4(-1, -1, -1, -1);
+        s_owner4[2 * tid + 1] = make_int4(-1, -1, -1, -1);
+        __syncthreads();
+        if (cnt > 0) {
+            if (my_start >= cb) {
+                if (my_start < cb + kEmitChunk) s_owner[my_start - cb] = tid;
+            } else if (my_start + cnt > cb) {
+                s_owner[0] = tid;  // the run that straddles the chunk boundary
+            }
         }
-        ushort4 b = s_box[lo];
-        int nv = (int)b.w - (int)b.z;
-        int cnt2 = ((int)b.y - (int)b.x) * nv;
-        unsigned int r = s - (s_end[lo] - (unsigned int)cnt2);
-        int tu = (int)b.x + (int)(r / (unsigned int)nv);
-        int tv = (int)b.z + (int)(r % (unsigned int)nv);
-        long long slot = (long long)base + s;
-        if (slot < k_total) {
-            tile_ids[slot] = (uint32_t)(tu + tv * tiles_per_row);
-            payload[slot] = s_row[lo];
+        __syncthreads();
+        int4 a = s_owner4[2 * tid], b = s_owner4[2 * tid + 1];
+        a.y = max(a.y, a.x);
+        a.z = max(a.z, a.y);
+        a.w = max(a.w, a.z);
+        b.x = max(b.x, a.w);
+        b.y = max(b.y, b.x);
+        b.z = max(b.z, b.y);
+        b.w = max(b.w, b.z);
+        int run = b.w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int o = __shfl_up_sync(0xffffffffu, run, d);
+            if (lane >= d) run = max(run, o);
         }
+        int before = __shfl_up_sync(0xffffffffu, run, 1);
+        if (lane == 0) before = -1;
+        if (lane == 31) s_warp_max[warp] = run;
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < kEmitBlock / 32; ++w)
+            if (w < warp) before = max(before, s_warp_max[w]);
+        a.x = max(a.x, before);
+        a.y = max(a.y, before);
+        a.z = max(a.z, before);
+        a.w = max(a.w, before);
+        b.x = max(b.x, before);
+        b.y = max(b.y, before);
+        b.z = max(b.z, before);
+        b.w = max(b.w, before);
+        s_owner4[2 * tid] = a;
+        s_owner4[2 * tid + 1] = b;
+        __syncthreads();
+#pragma unroll
+        for (int j = 0; j < kEmitChunk / kEmitBlock; ++j) {
+            const unsigned int ls = tid + kEmitBlock * j, sl = cb + ls;
+            const long long slot = (long long)base + sl;
+            if (sl < total && slot < k_total) {
+                const int o = s_owner[ls];
+                const ushort4 bx = s_box[o];
+                const unsigned int nv = (unsigned int)((int)bx.w - (int)bx.z);
+                const unsigned int r = sl - s_start[o];
+                // r / nv from a float estimate (|error| <= 1 for r < 2^22) and one correction
+                unsigned int q = (unsigned int)((float)r * s_rcp[o]);
+                int rem = (int)(r - q * nv);
+                if (rem < 0) {
+                    rem += (int)nv;
+                    --q;
+                } else if (rem >= (int)nv) {
+                    rem -= (int)nv;
+                    ++q;
+                }
+                tile_ids[slot] = (uint32_t)(((int)bx.x + (int)q) + ((int)bx.z + rem) * tiles_per_row);
+                payload[slot] = s_row[o];
+            }
+        }
+        __syncthreads();
     }
 }
 
