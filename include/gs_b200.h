@@ -108,8 +108,12 @@ int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *p
  *   -- the host can enqueue the sort before it has read the totals of gs_project_cull_sh back.
  * gs_emit_tile_keys: walks `order`, and for every tile of every point's bounding box writes
  *   tile_ids [k] u32 and payload [k] i32 (= row index), contiguous per point, points in `order`.
+ *   digit_hist (nullable) [4 * 256] u32: if given it is zeroed and receives, per 8-bit digit p of the
+ *   low key_bits bits, how many emitted ids have each digit value (bins p * 256 + value) -- the
+ *   histogram gs_sort_pairs32 would otherwise compute with one more pass over the ids.
  * gs_sort_pairs32: stable ascending sort of (u32 key, i32 payload) by the low `key_bits` bits;
- *   ping-pong buffers and *result_in_alt as gs_sort_pairs.
+ *   ping-pong buffers and *result_in_alt as gs_sort_pairs.  digit_hist (nullable): the digit
+ *   histogram of the keys in the layout above, if the caller already has it.
  * gs_tile_ranges32: as gs_tile_ranges, on sorted tile ids.
  * gs_sorted_keys: rebuilds the reference's sorted 64-bit keys (depth_key[payload] + (tile << 32),
  *   R.py:159-160) for inspection and the parity tests; not on the product path.
@@ -117,10 +121,11 @@ int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt, int32_t *p
 int gs_sort_points_by_depth(const int32_t *depth_key, int64_t m, const int64_t *m_dev, int depth_bits,
                             int32_t *order, void *workspace, void *stream);
 int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k, int width,
-                      uint32_t *tile_ids, int32_t *payload, void *workspace, void *stream);
+                      uint32_t *tile_ids, int32_t *payload, void *workspace, uint32_t *digit_hist,
+                      int key_bits, void *stream);
 int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_alt, int32_t *payload_alt,
-                    int64_t k, int key_bits, void *workspace, int *result_in_alt /*host*/,
-                    void *stream);
+                    int64_t k, int key_bits, void *workspace, const uint32_t *digit_hist,
+                    int *result_in_alt /*host*/, void *stream);
 int gs_tile_ranges32(const uint32_t *sorted_tile_ids, int64_t k, int32_t *tile_start,
                      int32_t *tile_end, int num_tiles, void *stream);
 int gs_sorted_keys(const uint32_t *sorted_tile_ids, const int32_t *sorted_payload,

@@ -409,14 +409,19 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         _mark("host_sync_and_alloc")
         st.keys = None
         if k > 0:
+            # the emission counts the tile-id digits while it writes them: the pair sort starts
+            # from that histogram instead of re-reading the K ids
+            digit_hist = torch.empty(4 * 256, dtype=torch.int32, device=dev)
             _capi.check(_lib.gs_emit_tile_keys(order.data_ptr(), buf.ptr("bbox"), m, k, W,
                                                tid2.data_ptr(), pay2.data_ptr(), sort_ws.data_ptr(),
-                                               stream), "gs_emit_tile_keys")
+                                               digit_hist.data_ptr(), max(tile_bits, 1), stream),
+                        "gs_emit_tile_keys")
             _mark("emit_keys")
             in_alt = C.c_int(0)
             _capi.check(_lib.gs_sort_pairs32(tid2.data_ptr(), pay2.data_ptr(),
                                              tid2.data_ptr() + 4 * kk, pay2.data_ptr() + 4 * kk, k,
-                                             tile_bits, sort_ws.data_ptr(), C.byref(in_alt), stream),
+                                             tile_bits, sort_ws.data_ptr(), digit_hist.data_ptr(),
+                                             C.byref(in_alt), stream),
                         "gs_sort_pairs32")
             _mark("sort_pairs")
             half = slice(kk, kk + k) if in_alt.value else slice(0, k)

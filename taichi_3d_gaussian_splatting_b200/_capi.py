@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
 
-ABI_VERSION = 105
+ABI_VERSION = 106
 
 _p = C.c_void_p
 _i = C.c_int
@@ -30,8 +30,8 @@ SIGNATURES = {
     "gs_point_sort_workspace_bytes": (_l, [_l]),
     "gs_emit_workspace_bytes": (_l, [_l]),
     "gs_sort_points_by_depth": (_i, [_p, _l, _p, _i, _p, _p, _p]),
-    "gs_emit_tile_keys": (_i, [_p, _p, _l, _l, _i, _p, _p, _p, _p]),
-    "gs_sort_pairs32": (_i, [_p, _p, _p, _p, _l, _i, _p, C.POINTER(C.c_int), _p]),
+    "gs_emit_tile_keys": (_i, [_p, _p, _l, _l, _i, _p, _p, _p, _p, _i, _p]),
+    "gs_sort_pairs32": (_i, [_p, _p, _p, _p, _l, _i, _p, _p, C.POINTER(C.c_int), _p]),
     "gs_tile_ranges32": (_i, [_p, _l, _p, _p, _i, _p]),
     "gs_sorted_keys": (_i, [_p, _p, _p, _l, _p, _p]),
     "gs_inverse_pose": (_i, [_p, _p, _i, _p, _p, _p]),

@@ -93,14 +93,21 @@ __global__ void tile_ranges_kernel(const long long *__restrict__ keys, long long
 constexpr unsigned long long kEmitAggregate = 1ull << 62;
 constexpr unsigned long long kEmitPrefix = 2ull << 62;
 constexpr int kEmitChunk = 2048;  // slots per owner scan: 8 per thread
+constexpr int kEmitHistPasses = 4;  // 32-bit tile ids: at most four 8-bit digits
 constexpr unsigned long long kEmitValueMask = (1ull << 62) - 1;
 
 __global__ void __launch_bounds__(kEmitBlock)
 emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ bbox, long long m,
                       long long k_total, int tiles_per_row, uint32_t *__restrict__ tile_ids,
                       int32_t *__restrict__ payload, unsigned long long *__restrict__ status,
-                      unsigned int *__restrict__ ticket)
+                      unsigned int *__restrict__ ticket, uint32_t *__restrict__ digit_hist,
+                      const int hist_passes)
 {
+    // digit histograms of the tile ids this CTA emits (what the pair sort's first kernel would
+    // otherwise re-read all K ids for): hist_passes x 256 bins of 8-bit digits, low digit first
+    __shared__ uint32_t s_hist[kEmitHistPasses * 256];
+    if (digit_hist)
+        for (int i = threadIdx.x; i < hist_passes * 256; i += kEmitBlock) s_hist[i] = 0;
     __shared__ unsigned int s_start[kEmitBlock];
     __shared__ float s_rcp[kEmitBlock];
     __shared__ __align__(16) int s_owner[kEmitChunk];
@@ -243,12 +250,18 @@ emit_tile_keys_kernel(const int32_t *__restrict__ order, const ushort4 *__restri
                     rem -= (int)nv;
                     ++q;
                 }
-                tile_ids[slot] = (uint32_t)(((int)bx.x + (int)q) + ((int)bx.z + rem) * tiles_per_row);
+                const uint32_t id = (uint32_t)(((int)bx.x + (int)q) + ((int)bx.z + rem) * tiles_per_row);
+                tile_ids[slot] = id;
                 payload[slot] = s_row[o];
+                if (digit_hist)
+                    for (int p = 0; p < hist_passes; ++p) atomicAdd(&s_hist[p * 256 + ((id >> (8 * p)) & 255u)], 1u);
             }
         }
         __syncthreads();
     }
+    if (digit_hist)
+        for (int i = tid; i < hist_passes * 256; i += kEmitBlock)
+            if (s_hist[i]) atomicAdd(digit_hist + i, s_hist[i]);
 }
 
 // four ids per thread (one 16-byte load when the array is 16-byte aligned) plus the successor
@@ -340,8 +353,11 @@ extern "C" int64_t gs_emit_workspace_bytes(int64_t m)
 
 extern "C" int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k,
                                  int width, uint32_t *tile_ids, int32_t *payload, void *workspace,
-                                 void *stream)
+                                 uint32_t *digit_hist, int key_bits, void *stream)
 {
+    if (digit_hist && (key_bits < 1 || key_bits > 32)) return GS_E_INVALID;
+    if (digit_hist)
+        GS_CUDA_TRY(cudaMemsetAsync(digit_hist, 0, sizeof(uint32_t) * 256 * kEmitHistPasses, (cudaStream_t)stream));
     if (m < 0 || k < 0 || width <= 0 || width % kTile) return GS_E_INVALID;
     if (k >= (1ll << 31)) return GS_E_CAPACITY;  // int32 indices downstream (R.py:930, 954-957)
     if (m == 0 || k == 0) return GS_OK;
@@ -352,7 +368,7 @@ extern "C" int gs_emit_tile_keys(const int32_t *order, const uint16_t *bbox, int
     unsigned long long *status = (unsigned long long *)workspace;
     emit_tile_keys_kernel<<<blocks, kEmitBlock, 0, st>>>(
         order, reinterpret_cast<const ushort4 *>(bbox), m, k, width / kTile, tile_ids, payload, status,
-        (unsigned int *)(status + blocks));
+        (unsigned int *)(status + blocks), digit_hist, digit_hist ? (key_bits + 7) / 8 : 0);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -54,8 +54,22 @@ histogram_kernel(const KeyT *__restrict__ keys, long long k, const long long *__
     __shared__ uint32_t sh[kMaxPasses * kRadix];
     for (int i = threadIdx.x; i < num_passes * kRadix; i += blockDim.x) sh[i] = 0;
     __syncthreads();
-    long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < k; i += stride) {
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const long long tid0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    // four independent loads in flight per thread (the loop is latency bound otherwise)
+    long long i = tid0;
+    for (; i + 3 * stride < k; i += 4 * stride) {
+        KeyT q[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) q[j] = keys[i + j * stride];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            auto c = compact_key(q[j], spec);
+            for (int p = 0; p < num_passes; ++p)
+                atomicAdd(&sh[p * kRadix + (int)((c >> (8 * p)) & 0xff)], 1u);
+        }
+    }
+    for (; i < k; i += stride) {
         auto c = compact_key(keys[i], spec);
         for (int p = 0; p < num_passes; ++p)
             atomicAdd(&sh[p * kRadix + (int)((c >> (8 * p)) & 0xff)], 1u);
@@ -305,7 +319,8 @@ inline int64_t sort_tiles(int64_t k) { return (k + kSortTile - 1) / kSortTile; }
 template <typename KeyT>
 int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, int32_t *vals_a,
               KeyT *keys_b, int32_t *vals_b, int64_t k, const KeySpec &spec, int total_bits,
-              void *workspace, cudaStream_t st, const long long *k_dev = nullptr)
+              void *workspace, cudaStream_t st, const long long *k_dev = nullptr,
+              const uint32_t *ready_hist = nullptr)
 {
     const int num_passes = (total_bits + 7) / 8;
     const int64_t tiles = sort_tiles(k);
@@ -330,11 +345,13 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
         attr_set = true;
     }
 
-    int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
-    if (hist_blocks < 1) hist_blocks = 1;
-    histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, k_dev, spec, num_passes, ghist);
-    GS_LAUNCH_CHECK();
-    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ghist, gbase);
+    if (!ready_hist) {  // else: the producer of the keys counted the digits while writing them
+        int hist_blocks = (int)min((int64_t)148 * 8, (k + 256 * 8 - 1) / (256 * 8));
+        if (hist_blocks < 1) hist_blocks = 1;
+        histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, k_dev, spec, num_passes, ghist);
+        GS_LAUNCH_CHECK();
+    }
+    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ready_hist ? ready_hist : ghist, gbase);
     GS_LAUNCH_CHECK();
 
     const KeyT *kin = keys_first;
@@ -404,7 +421,7 @@ extern "C" int gs_sort_pairs(int64_t *keys, int32_t *payload, int64_t *keys_alt,
 
 extern "C" int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_alt,
                                int32_t *payload_alt, int64_t k, int key_bits, void *workspace,
-                               int *result_in_alt, void *stream)
+                               const uint32_t *digit_hist, int *result_in_alt, void *stream)
 {
     if (result_in_alt) *result_in_alt = 0;
     if (k < 0 || key_bits < 0 || key_bits > 32) return GS_E_INVALID;
@@ -414,7 +431,7 @@ extern "C" int gs_sort_pairs32(uint32_t *keys, int32_t *payload, uint32_t *keys_
     KeySpec spec = {32, 0xffffffffull, 0ull};
     int num_passes = (key_bits + 7) / 8;
     int rc = sort_impl<unsigned int>(keys, payload, keys_alt, payload_alt, keys, payload, k, spec,
-                                     key_bits, workspace, (cudaStream_t)stream);
+                                     key_bits, workspace, (cudaStream_t)stream, nullptr, digit_hist);
     if (rc != GS_OK) return rc;
     if (result_in_alt) *result_in_alt = (num_passes & 1);
     return GS_OK;

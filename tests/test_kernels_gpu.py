@@ -76,7 +76,7 @@ def test_sort_pairs32_stable(k, bits):
     ws = torch.empty(int(capi.lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
     in_alt = C.c_int(0)
     capi.check(capi.lib.gs_sort_pairs32(keys.data_ptr(), vals.data_ptr(), keys_alt.data_ptr(),
-                                        vals_alt.data_ptr(), k, bits, ws.data_ptr(), C.byref(in_alt),
+                                        vals_alt.data_ptr(), k, bits, ws.data_ptr(), None, C.byref(in_alt),
                                         torch.cuda.current_stream().cuda_stream), "gs_sort_pairs32")
     torch.cuda.synchronize()
     rk, rv = (keys_alt, vals_alt) if in_alt.value else (keys, vals)
@@ -143,11 +143,43 @@ def test_emit_tile_keys_follows_the_given_order():
     pay = torch.empty(k, dtype=torch.int32, device=dev)
     ws = torch.empty(int(capi.lib.gs_emit_workspace_bytes(m)), dtype=torch.uint8, device=dev)
     st = torch.cuda.current_stream().cuda_stream
+    tile_bits = max(int(tw * th - 1).bit_length(), 1)
+    hist = torch.full((4 * 256,), -1, dtype=torch.int32, device=dev)   # the call zeroes it
     capi.check(capi.lib.gs_emit_tile_keys(d_order.data_ptr(), d_bbox.data_ptr(), m, k, W, ids.data_ptr(),
-                                          pay.data_ptr(), ws.data_ptr(), st), "gs_emit_tile_keys")
+                                          pay.data_ptr(), ws.data_ptr(), hist.data_ptr(), tile_bits, st),
+               "gs_emit_tile_keys")
     torch.cuda.synchronize()
     assert np.array_equal(ids.cpu().numpy(), np.asarray(ids_ref, np.int32))
     assert np.array_equal(pay.cpu().numpy(), np.asarray(pay_ref, np.int32))
+    # the digit histogram handed to the pair sort: exact counts per 8-bit digit, unused digits zero
+    h = hist.cpu().numpy().reshape(4, 256)
+    ref_ids = np.asarray(ids_ref, np.uint32)
+    for p in range(4):
+        want = np.bincount((ref_ids >> (8 * p)) & 255, minlength=256) if 8 * p < tile_bits else np.zeros(256, int)
+        assert np.array_equal(h[p], want), p
+    # sorting with that histogram gives the same result as sorting without it
+    outs = []
+    for use_hist in (False, True):
+        k2 = torch.cat([ids, torch.empty_like(ids)])
+        v2 = torch.cat([pay, torch.empty_like(pay)])
+        sws = torch.empty(int(capi.lib.gs_sort_workspace_bytes(k)), dtype=torch.uint8, device=dev)
+        in_alt = C.c_int(0)
+        capi.check(capi.lib.gs_sort_pairs32(k2.data_ptr(), v2.data_ptr(), k2.data_ptr() + 4 * k,
+                                            v2.data_ptr() + 4 * k, k, tile_bits, sws.data_ptr(),
+                                            hist.data_ptr() if use_hist else None, C.byref(in_alt), st),
+                   "gs_sort_pairs32")
+        torch.cuda.synchronize()
+        half = slice(k, 2 * k) if in_alt.value else slice(0, k)
+        outs.append((k2[half].cpu().numpy(), v2[half].cpu().numpy()))
+    assert np.array_equal(outs[0][0], outs[1][0]) and np.array_equal(outs[0][1], outs[1][1])
+    order_ref = np.argsort(ref_ids, kind="stable")
+    assert np.array_equal(outs[1][1], np.asarray(pay_ref, np.int32)[order_ref])
+    # without a histogram buffer the emission is unchanged
+    ids_b = torch.empty_like(ids)
+    capi.check(capi.lib.gs_emit_tile_keys(d_order.data_ptr(), d_bbox.data_ptr(), m, k, W, ids_b.data_ptr(),
+                                          pay.data_ptr(), ws.data_ptr(), None, 0, st), "gs_emit_tile_keys")
+    torch.cuda.synchronize()
+    assert torch.equal(ids_b, ids)
     sorted_ids = torch.sort(ids.to(torch.int64)).values.to(torch.int32)
     start = torch.empty(tw * th, dtype=torch.int32, device=dev)
     end = torch.empty(tw * th, dtype=torch.int32, device=dev)
