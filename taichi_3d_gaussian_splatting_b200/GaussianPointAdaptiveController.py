@@ -35,8 +35,6 @@ class AdaptiveControllerAccumulators:
     def __init__(self, num_points: int, device):
         self.num_points = int(num_points)
         self.device = torch.device(device)
-        if self.device.type != "cuda":
-            raise ValueError("the accumulators live on a CUDA device")
         self.iteration_counter = -1
         self.reset()
 
@@ -49,6 +47,8 @@ class AdaptiveControllerAccumulators:
     @torch.no_grad()
     def update(self, input_data) -> None:
         """`input_data`: the BackwardValidPointHookInput of one backward (R.py:806-817)."""
+        if self.device.type != "cuda":
+            raise ValueError("update() runs a CUDA kernel: the accumulators must live on a CUDA device")
         self.iteration_counter += 1
         ids = input_data.point_id_in_camera_list
         m = int(ids.shape[0])
@@ -69,3 +69,14 @@ class AdaptiveControllerAccumulators:
                 self.accumulated_position_gradients.data_ptr(),
                 self.accumulated_position_gradients_norm.data_ptr(),
                 torch.cuda.current_stream(self.device).cuda_stream), "gs_controller_accumulate")
+
+    def all_reduce(self, group=None) -> None:
+        """View-sharded training (distributed.ViewShardedTrainerStep): every rank has accumulated the
+        statistics of ITS views; summing them over the ranks gives what a single process that saw
+        every view would hold.  Call it before the densification policy reads the tensors (once per
+        densification interval, not per step)."""
+        import torch.distributed as dist
+        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+            return
+        for name, _, _ in self.FIELDS:
+            dist.all_reduce(getattr(self, name), group=group)

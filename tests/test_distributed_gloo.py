@@ -151,3 +151,39 @@ def test_two_rank_fused_accumulation_matches_plain_step():
         assert torch.allclose(gf, feat.grad, rtol=1e-4, atol=1e-4)
         assert torch.allclose(loss, res.loss, rtol=1e-5)
     assert torch.equal(out[0][0], out[1][0]) and torch.equal(out[0][1], out[1][1])
+
+
+def _stats_worker(rank, world, port, n, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from taichi_3d_gaussian_splatting_b200.GaussianPointAdaptiveController import AdaptiveControllerAccumulators
+    acc = AdaptiveControllerAccumulators(n, "cpu")   # holding and exchanging needs no GPU; update() does
+    g = torch.Generator().manual_seed(100 + rank)
+    for name, dtype, _ in acc.FIELDS:
+        t = getattr(acc, name)
+        if dtype == torch.int32:
+            t.copy_(torch.randint(0, 50, t.shape, generator=g, dtype=torch.int32))
+        else:
+            t.copy_(torch.rand(t.shape, generator=g))
+    before = {name: getattr(acc, name).clone() for name, _, _ in acc.FIELDS}
+    acc.all_reduce()
+    out[rank] = (before, {name: getattr(acc, name).clone() for name, _, _ in acc.FIELDS})
+    dist.destroy_process_group()
+
+
+@pytest.mark.timeout(300)
+def test_densification_statistics_are_summed_over_ranks():
+    """SURVEY.md section 8(f) row 2, multi-GPU half: each rank accumulates the statistics of its own
+    views; all_reduce() gives every rank the totals."""
+    n, world = 300, 2
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_stats_worker, args=(world, _free_port(), n, out), nprocs=world, join=True)
+        out = dict(out)
+    for name in out[0][0]:
+        total = out[0][0][name] + out[1][0][name]
+        assert torch.equal(out[0][1][name], out[1][1][name])
+        if total.dtype == torch.int32:
+            assert torch.equal(out[0][1][name], total)
+        else:
+            assert torch.allclose(out[0][1][name], total, rtol=1e-6)
