@@ -314,19 +314,28 @@ def run_b200(args):
             ev.record(copy_stream)
         return q, t, wt_stage[slot], ev
 
+    prefetched = {}  # step index -> upload of its first view, started during the previous step
+
     def step_e2e(i):
         cur = torch.cuda.current_stream(dev)
         flat.zero_()
         total = torch.zeros((), device=dev)
-        copy_stream.wait_stream(cur)        # staging buffers of the previous step are free
-        nxt = upload(view_of(i, 0), 0)
+        nxt = prefetched.pop(i, None)
+        if nxt is None:
+            copy_stream.wait_stream(cur)    # staging buffers of the previous step are free
+            nxt = upload(view_of(i, 0), 0)
         for j in range(VIEWS_PER_RANK):
             q, t, wt, ev = nxt
-            if j + 1 < VIEWS_PER_RANK:      # prefetch the next view while this one renders
-                done = torch.cuda.Event()
-                done.record(cur)            # ...once the slot's previous reader has been enqueued
-                copy_stream.wait_event(done)
+            # prefetch the next view (of this step, or the first of the next one: a trainer's loader
+            # runs ahead across steps too) while this one renders, once the slot's previous reader
+            # has been enqueued
+            done = torch.cuda.Event()
+            done.record(cur)
+            copy_stream.wait_event(done)
+            if j + 1 < VIEWS_PER_RANK:
                 nxt = upload(view_of(i, j + 1), (j + 1) & 1)
+            else:
+                prefetched[i + 1] = upload(view_of(i + 1, 0), VIEWS_PER_RANK & 1)
             cur.wait_event(ev)
             total += render_loss(q, t, wt)
         finish_step()
