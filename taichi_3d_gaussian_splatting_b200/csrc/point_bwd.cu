@@ -212,13 +212,18 @@ __global__ void __launch_bounds__(128) point_bwd_kernel(PointBwdParams p)
     float4 *rows = s_rows[warp];
     const int half = lane >> 4, col = lane & 15;
 
+    // asynchronous 16-byte copies (LDGSTS): the warp's 448 loads are all in flight at once and
+    // never pass through registers
 #pragma unroll 8
     for (int r = 0; r < 32; r += 2) {
         const long long rpid = __shfl_sync(0xffffffffu, pid, r + half);
-        if (col < 14 && rpid >= 0)
-            rows[(r + half) * kRowStride4 + col] =
-                __ldg(reinterpret_cast<const float4 *>(p.features + (size_t)GS_FEATURES * rpid) + col);
+        if (col < 14 && rpid >= 0) {
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(rows + (r + half) * kRowStride4 + col);
+            const float4 *src = reinterpret_cast<const float4 *>(p.features + (size_t)GS_FEATURES * rpid) + col;
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+        }
     }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
     __syncwarp();
     if (valid) point_chain(p, idx, pid, rows + lane * kRowStride4);
     __syncwarp();
