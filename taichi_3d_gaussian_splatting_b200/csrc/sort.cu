@@ -81,11 +81,16 @@ histogram_kernel(const KeyT *__restrict__ keys, long long k, const long long *__
 
 // exclusive scan of each pass's 256-bin histogram; one block of 256 threads per pass
 __global__ void __launch_bounds__(256)
-scan_histogram_kernel(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ gbase)
+scan_histogram_kernel(const uint32_t *__restrict__ ghist, uint32_t *__restrict__ gbase, long long k,
+                      const long long *__restrict__ k_dev, unsigned int *__restrict__ trivial)
 {
     __shared__ uint32_t s_warp[kSortWarps];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (k_dev) k = *k_dev;
     uint32_t v = ghist[blockIdx.x * kRadix + tid];
+    // every key has the same digit in this pass: the pass is the identity permutation and the
+    // onesweep kernel only copies (e.g. the top pass of depth keys far below the far plane)
+    if (k > 0 && (long long)v == k) trivial[blockIdx.x] = 1u;
     uint32_t incl = v;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -109,7 +114,7 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
                 KeyT *__restrict__ keys_out, int32_t *__restrict__ vals_out, long long k,
                 const long long *__restrict__ k_dev, KeySpec spec, int shift, int digit_bits,
                 const uint32_t *__restrict__ gbase, uint32_t *__restrict__ status,
-                unsigned int *__restrict__ ticket)
+                unsigned int *__restrict__ ticket, const unsigned int *__restrict__ trivial)
 {
     if (k_dev) k = *k_dev;  // launched for a capacity: tiles past the real count leave at once
     extern __shared__ __align__(16) unsigned char smem[];
@@ -158,6 +163,18 @@ onesweep_kernel(const KeyT *__restrict__ keys_in, const int32_t *__restrict__ va
                 val[j] = 0;
             }
         }
+    }
+
+    if (*trivial) {  // identity pass (see scan_histogram_kernel): element i stays at i
+#pragma unroll
+        for (int j = 0; j < kItems; ++j) {
+            const int local = warp_first + j * 32 + lane;
+            if (local < valid) {
+                keys_out[tile_base + local] = key[j];
+                vals_out[tile_base + local] = val[j];
+            }
+        }
+        return;
     }
 
     // ---- warp-level stable ranking per digit (match.any) ---------------------------------
@@ -351,7 +368,8 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
         histogram_kernel<KeyT><<<hist_blocks, 256, 0, st>>>(keys_first, k, k_dev, spec, num_passes, ghist);
         GS_LAUNCH_CHECK();
     }
-    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ready_hist ? ready_hist : ghist, gbase);
+    scan_histogram_kernel<<<num_passes, 256, 0, st>>>(ready_hist ? ready_hist : ghist, gbase, k, k_dev,
+                                                      tickets + kMaxPasses);
     GS_LAUNCH_CHECK();
 
     const KeyT *kin = keys_first;
@@ -363,11 +381,11 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
         if (ballot)
             onesweep_kernel<KeyT, true><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
                 kin, vin, kout, vout, k, k_dev, spec, 8 * p, digit_bits, gbase + p * kRadix,
-                status + (size_t)p * tiles * kRadix, tickets + p);
+                status + (size_t)p * tiles * kRadix, tickets + p, tickets + kMaxPasses + p);
         else
             onesweep_kernel<KeyT, false><<<(unsigned)tiles, kSortBlock, sort_smem(sizeof(KeyT)), st>>>(
                 kin, vin, kout, vout, k, k_dev, spec, 8 * p, digit_bits, gbase + p * kRadix,
-                status + (size_t)p * tiles * kRadix, tickets + p);
+                status + (size_t)p * tiles * kRadix, tickets + p, tickets + kMaxPasses + p);
         GS_LAUNCH_CHECK();
         kin = kout;
         vin = vout;
