@@ -57,6 +57,8 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2_1m_1920x1088", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--lanes", type=int, default=2,
+                    help="CUDA streams the views of a step are spread over (view j on lane j mod L)")
     return ap.parse_args()
 
 
@@ -276,7 +278,6 @@ def run_b200(args):
     gx, gf = flat[:3 * n].view(n, 3), flat[3 * n:].view(n, 56)
     ras.accumulate_gradients_into(gx, gf)
     copy_stream = torch.cuda.Stream(dev)
-    wt_stage = [torch.empty_like(wt_dev) for _ in range(2)]   # e2e: double-buffered target upload
 
     def view_of(step, j):  # global view index of this rank's j-th view of the step
         return ((step * world + rank) * VIEWS_PER_RANK + j) % NUM_VIEWS
@@ -295,49 +296,97 @@ def run_b200(args):
             dist.all_reduce(flat)
         xyz.grad, feat.grad = gx, gf
 
+    lanes = max(1, min(args.lanes, VIEWS_PER_RANK))
+    lane_streams = [torch.cuda.Stream(dev) for _ in range(lanes)] if lanes > 1 else []
+
+    def run_views(per_view, use_lanes=True):
+        """The step's views, view j on lane j mod L (the views are independent: their gradients are
+        summed into `flat` by RED either way).  The hot kernels are issue-bound, the key pipeline is
+        latency / HBM bound: two views in flight fill each other's idle slots."""
+        cur = torch.cuda.current_stream(dev)
+        if not (use_lanes and lane_streams):
+            total = torch.zeros((), device=dev)
+            for j in range(VIEWS_PER_RANK):
+                total += per_view(j, cur)
+            return total
+        start = torch.cuda.Event()
+        start.record(cur)
+        totals = []
+        for s in lane_streams:
+            s.wait_event(start)
+            with torch.cuda.stream(s):
+                totals.append(torch.zeros((), device=dev))
+        for j in range(VIEWS_PER_RANK):
+            s = lane_streams[j % lanes]
+            with torch.cuda.stream(s):
+                totals[j % lanes] += per_view(j, s)
+        for s in lane_streams:
+            e = torch.cuda.Event()
+            e.record(s)
+            cur.wait_event(e)
+        return torch.stack(totals).sum()
+
+    def resident_view(i):
+        def per_view(j, stream):
+            v = view_of(i, j)
+            return render_loss(qs_dev[v:v + 1], ts_dev[v:v + 1], wt_dev)
+        return per_view
+
     def step_resident(i):
         flat.zero_()
-        total = torch.zeros((), device=dev)
-        for j in range(VIEWS_PER_RANK):
-            v = view_of(i, j)
-            total += render_loss(qs_dev[v:v + 1], ts_dev[v:v + 1], wt_dev)
+        total = run_views(resident_view(i))
         finish_step()
         return total
 
-    def upload(v, slot):
-        """pose + target of view v from pinned host memory, on the copy stream"""
+    def step_resident_single_stream(i):  # the instrumented pass: per-stage CUDA events need one stream
+        flat.zero_()
+        total = run_views(resident_view(i), use_lanes=False)
+        finish_step()
+        return total
+
+    num_slots = 2 * lanes                                      # e2e: staging buffers of the targets
+    wt_stage = [torch.empty_like(wt_dev) for _ in range(num_slots)]
+    uploads, finished, next_upload = {}, {}, [0]
+
+    def upload(g):
+        """pose + target of the g-th view this rank renders, from pinned host memory, on the copy
+        stream, into staging slot g mod num_slots (free once view g - num_slots has been rendered)"""
+        v = view_of(g // VIEWS_PER_RANK, g % VIEWS_PER_RANK)
+        slot = g % num_slots
         with torch.cuda.stream(copy_stream):
+            prev = finished.pop(g - num_slots, None)
+            if prev is not None:
+                copy_stream.wait_event(prev)
             q = qs_host[v:v + 1].to(dev, non_blocking=True)
             t = ts_host[v:v + 1].to(dev, non_blocking=True)
             wt_stage[slot].copy_(wt_host, non_blocking=True)
             ev = torch.cuda.Event()
             ev.record(copy_stream)
-        return q, t, wt_stage[slot], ev
-
-    prefetched = {}  # step index -> upload of its first view, started during the previous step
+        uploads[g] = (q, t, wt_stage[slot], ev)
 
     def step_e2e(i):
-        cur = torch.cuda.current_stream(dev)
         flat.zero_()
-        total = torch.zeros((), device=dev)
-        nxt = prefetched.pop(i, None)
-        if nxt is None:
-            copy_stream.wait_stream(cur)    # staging buffers of the previous step are free
-            nxt = upload(view_of(i, 0), 0)
-        for j in range(VIEWS_PER_RANK):
-            q, t, wt, ev = nxt
-            # prefetch the next view (of this step, or the first of the next one: a trainer's loader
-            # runs ahead across steps too) while this one renders, once the slot's previous reader
-            # has been enqueued
+        if next_upload[0] < i * VIEWS_PER_RANK or not uploads:   # first call: nothing prefetched yet
+            copy_stream.wait_stream(torch.cuda.current_stream(dev))
+            uploads.clear()
+            finished.clear()
+            next_upload[0] = i * VIEWS_PER_RANK
+
+        def per_view(j, stream):
+            g = i * VIEWS_PER_RANK + j
+            # the loader runs `lanes` views ahead of the renderer, across step boundaries too
+            while next_upload[0] <= g + lanes:
+                upload(next_upload[0])
+                next_upload[0] += 1
+            q, t, wt, ev = uploads.pop(g)
+            stream.wait_event(ev)
+            loss = render_loss(q, t, wt)
             done = torch.cuda.Event()
-            done.record(cur)
-            copy_stream.wait_event(done)
-            if j + 1 < VIEWS_PER_RANK:
-                nxt = upload(view_of(i, j + 1), (j + 1) & 1)
-            else:
-                prefetched[i + 1] = upload(view_of(i + 1, 0), VIEWS_PER_RANK & 1)
-            cur.wait_event(ev)
-            total += render_loss(q, t, wt)
+            done.record(stream)
+            finished[g] = done
+            return loss
+
+        total = run_views(per_view)
         finish_step()
         return float(total.item())  # device -> host read of the step's result
 
@@ -376,8 +425,13 @@ def run_b200(args):
     prof = StageProfiler()
     timed(step_resident, 0, warmup)            # untimed warm-up (allocator, module load)
     sampler.start()
-    impl.STAGE_PROFILER = prof if rank == 0 else None
     ms_resident = timed(step_resident, args.steps, 0)
+    # per-stage CUDA-event times (stages, roofline): the same steps once more on ONE stream, because
+    # events bracket a stage only when nothing else is in flight (all ranks run it: all-reduce inside)
+    stage_steps = min(args.steps, 10)
+    timed(step_resident_single_stream, 0, 1)
+    impl.STAGE_PROFILER = prof if rank == 0 else None
+    ms_single_stream = timed(step_resident_single_stream, stage_steps, 0)
     stage_ms = prof.summary() if rank == 0 else {}
     impl.STAGE_PROFILER = None
     ms_e2e = timed(step_e2e, args.steps, warmup)
@@ -463,6 +517,10 @@ def run_b200(args):
                    "step": f"{VIEWS_PER_RANK} views forward+backward per rank, gradients summed in "
                            "place, one all-reduce; an iteration (it) = one view forward+backward",
                    "views_per_rank_per_step": VIEWS_PER_RANK,
+                   "lanes": lanes,
+                   "lanes_note": f"view j of a step runs on CUDA stream j mod {lanes}; `stages` / `roofline` are "
+                                 f"timed in a separate single-stream pass of {stage_steps} steps "
+                                 f"({ms_single_stream / stage_steps:.3f} ms per step there)",
                    "key_pipeline": info.get("key_pipeline"),
                    "parallelism": f"views sharded over {world} rank(s), replicated cloud"
                                   + (", NCCL all-reduce of the Nx59 gradient per step" if world > 1 else ""),

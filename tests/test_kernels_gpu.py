@@ -459,3 +459,32 @@ def test_accumulate_gradients_into_sums_views():
         assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
     with pytest.raises(ValueError):
         ras.accumulate_gradients_into(gx[:, :2], gf)
+
+
+def test_view_sharded_step_on_two_lanes_matches_one_lane():
+    """distributed.ViewShardedTrainerStep with the fused accumulation: six views spread over two CUDA
+    streams give the gradient of the one-stream run (up to the order of the RED adds)."""
+    from taichi_3d_gaussian_splatting_b200.distributed import ViewShardedTrainerStep
+    scene = make_scene(20000, 256, 160, seed=23, scale_factor=0.02)
+    g = torch.from_numpy(np.random.default_rng(4).uniform(0, 1, (160, 256, 3)).astype(np.float32)).cuda()
+    views = [(0.01 * i, -0.005 * i) for i in range(6)]
+    results = []
+    for lanes in (1, 2, 3):
+        ras = _module()
+        t = util.scene_tensors(scene, requires_grad=True)
+
+        def render(xyz, feat, view, t=t, ras=ras):
+            t["t_pointcloud_camera"] = torch.tensor([[view[0], view[1], 0.0]], device="cuda")
+            image, _, _ = _call(ras, scene, t, band=3)
+            return image
+
+        step = ViewShardedTrainerStep(render, lambda image, view: (image * g).sum(), rasteriser=ras, lanes=lanes)
+        res = step(t["point_cloud"], t["point_cloud_features"], views)
+        torch.cuda.synchronize()
+        assert res.num_local_views == 6
+        results.append((t["point_cloud"].grad.clone(), t["point_cloud_features"].grad.clone(), float(res.loss)))
+    for gx, gf, loss in results[1:]:
+        assert abs(loss - results[0][2]) <= 1e-5 * abs(results[0][2])
+        for got, want in ((gx, results[0][0]), (gf, results[0][1])):
+            l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
+            assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
