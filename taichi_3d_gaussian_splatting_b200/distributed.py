@@ -42,7 +42,7 @@ class ViewShardedTrainerStep:
     def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
                  loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
                  group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True,
-                 rasteriser: Any = None, lanes: int = 2):
+                 rasteriser: Any = None, lanes: int = 4):
         """rasteriser: the GaussianPointCloudRasterisation module `render` calls, if the step should
         use its fused accumulation (`accumulate_gradients_into`): every view's backward then adds
         into one flat N x 59 buffer (no per-view zero fill, no AccumulateGrad pass) and the exchange
@@ -50,7 +50,7 @@ class ViewShardedTrainerStep:
         lanes: with the fused accumulation on a CUDA device, this rank's views are spread over that many
         CUDA streams (view j on lane j mod lanes).  The views are independent (their gradients meet only
         in the RED adds into the flat buffer), the blend kernels are issue-bound and the key pipeline is
-        latency / HBM bound, so two views in flight fill each other's idle slots (+8 % at 1M points,
+        latency / HBM bound, so views in flight fill each other's idle slots (+8 % with 2 lanes, +10 % with 4 at 1M points,
         1920x1088; tools/exp_two_streams.py).  The sum order of the gradient then varies from run to
         run (differences of 1e-7 relative)."""
         self.lanes = max(1, int(lanes))
