@@ -258,19 +258,22 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         __syncwarp();
 
         unsigned pending = __ballot_sync(0xffffffffu, my_mask != 0u);
+        const unsigned irregular = __ballot_sync(0xffffffffu, (my_mask & kCellMaskIrregular) != 0u);
         while (pending) {
             const int k = __ffs(pending) - 1;
             pending &= pending - 1u;
-            const unsigned mk = __shfl_sync(0xffffffffu, my_mask, k);
-            const unsigned m = mk & open;
-            if (m == 0u) continue;  // warp-uniform
+            unsigned m = 1u;  // one pair cell per warp: a pending entry is an entry of that cell
+            if (kPairs > 1) {
+                m = __shfl_sync(0xffffffffu, my_mask, k) & open;
+                if (m == 0u) continue;  // warp-uniform
+            }
             const float4 r0 = s_rec[3 * k];      // u v a b
             const float4 r1 = s_rec[3 * k + 1];  // c rescale alpha red
             const float4 r2 = s_rec[3 * k + 2];  // green blue z pad
             const float dx = fx - r0.x;
             const float dxdxa = dx * dx * r0.z;
             const int idx1 = base + k + 1;
-            if (mk & kCellMaskIrregular) {  // warp-uniform, rare
+            if ((irregular >> k) & 1u) {  // warp-uniform, rare
 #pragma unroll
                 for (int c = 0; c < kPairs; ++c)
                     if ((m >> c) & 1u)
