@@ -141,7 +141,7 @@ def stage_bytes(n, m, k, tiles, hw, info):
             # argsort of M 4-byte depth keys: histogram read + per pass key/value read and write
             "sort_points": m * (4 + 16 * pm - 4),
             "emit_keys": 12 * m + 8 * k,            # order + bbox in, tile id + payload out
-            "sort_pairs": k * (4 + 16 * pk),         # histogram read + per pass 8 B in, 8 B out
+            "sort_pairs": k * (16 * pk),             # per pass 8 B in, 8 B out (histogram: from the emission)
             "tile_ranges": 4 * k + 8 * tiles,
         }
     else:

@@ -1,7 +1,9 @@
 #!/usr/bin/env python
 """Aggregate an ncu report's per-instruction counters by CUDA source line.
 
-    python tools/ncu_by_line.py <report.ncu-rep> <kernel-regex> <cubin> <mangled-substring> [top]
+    python tools/ncu_by_line.py <report.ncu-rep> <kernel-regex> <cubin> <mangled-substring> [top] [launch]
+
+`launch` picks the n-th matching launch of the report (default 0).
 
 ncu's `--page source --csv` lists SASS instructions in program order with executed counts and
 stall samples; `nvdisasm -g -c` lists the same instructions with `//## File ..., line N` marks.
@@ -21,7 +23,8 @@ def main():
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name",
                           f"regex:{kregex}"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
-    hdr_i = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+    launch = int(sys.argv[6]) if len(sys.argv) > 6 else 0
+    hdr_i = [i for i, r in enumerate(rows) if r and r[0] == "Address"][launch]
     hdr = rows[hdr_i]
     body = []
     for r in rows[hdr_i + 1:]:
