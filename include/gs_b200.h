@@ -142,11 +142,16 @@ int gs_tile_ranges(const int64_t *sorted_keys, int64_t k, int32_t *tile_start, i
  * Forward blend.  Replaces gaussian_point_rasterisation (R.py:318-485).
  * image [H,W,3], depth [H,W], acc_alpha [H,W], last_effective [H,W] i32, valid_count [H,W] i32.
  * Every pixel is written (empty tiles give zeros).  With rgb_only != 0 only image is written.
+ * cell_masks (nullable) [4, mask_stride] u8, mask_stride >= k: for every list entry the forward
+ * visits, which 8x4-pixel cells of each 8x8 quarter of its tile the splat can reach (plane
+ * q = 2 * column + row half; bit 0 = upper cell, bit 1 = lower).  gs_blend_bwd takes the same
+ * buffer and then skips its own culling arithmetic; entries the forward never reached (every
+ * pixel of the quarter already saturated) are left unwritten and are not read.
  */
 int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
                  const int32_t *sorted_payload, const float *records, float *image, float *depth,
                  float *acc_alpha, int32_t *last_effective, int32_t *valid_count, int rgb_only,
-                 void *stream);
+                 uint8_t *cell_masks, int64_t mask_stride, void *stream);
 
 /*
  * Backward blend.  Replaces loop 1 of gaussian_point_rasterisation_backward (R.py:531-705).
@@ -154,12 +159,13 @@ int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t
  *   0:duv.u 1:duv.v 2:dcov00 3:dcov01 4:dcov11 5:dr 6:dg 7:db 8:dlogit 9:|duv| 10:#pixels(as float) 11:0
  * map_on_image [H,W,2] gets the per-pixel sum of |duv| (R.py:700-704).  It may be null: the
  * magnitudes (the map and slot 9) are observable only through the reference's backward hook, and
- * a caller without one skips them (slot 9 then stays 0).
+ * a caller without one skips them (slot 9 then stays 0).  cell_masks (nullable): what
+ * gs_blend_fwd wrote for the same tile lists.
  */
 int gs_blend_bwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
                  const int32_t *sorted_payload, const float *records, const float *image_grad,
                  const float *acc_alpha, const int32_t *last_effective, float *splat_grads,
-                 float *map_on_image, void *stream);
+                 float *map_on_image, const uint8_t *cell_masks, int64_t mask_stride, void *stream);
 
 /*
  * Per-point chain rule + SH band mask + factor scaling.  Replaces loop 2 of the backward kernel

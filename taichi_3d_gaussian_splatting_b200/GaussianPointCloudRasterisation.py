@@ -44,6 +44,10 @@ _GRAD_SLOTS = 12
 # 64-bit keys (R.py:131-172, 947-950); also taken automatically when depth keys can be negative.
 KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "depth_first")
 
+# the backward blend reuses the culling bits the forward blend computed (4 bytes per list entry kept
+# between forward and backward); 0 makes it recompute them
+REUSE_CELL_MASKS = os.environ.get("GS_REUSE_CELL_MASKS", "1") != "0"
+
 # set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
 STAGE_PROFILER = None
 
@@ -195,7 +199,8 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                 cfg = outer.config
                 out = _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask,
                                     point_object_id, q_pointcloud_camera, t_pointcloud_camera,
-                                    camera_info)
+                                    camera_info,
+                                    keep_cell_masks=ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
                 outer.last_forward_info = out.info
                 ctx.set_materialize_grads(False)
                 ctx.camera_info = camera_info
@@ -284,7 +289,7 @@ class _ForwardState:
     """Everything the backward needs, plus handles a test can read every stage from."""
     __slots__ = ("n", "m", "k", "width", "height", "buffers", "payload", "keys", "tile_start",
                  "tile_end", "image", "depth", "count", "acc_alpha", "last", "q_cam", "t_cam",
-                 "intrinsics", "info", "unsorted_keys", "unsorted_payload", "tile_ids")
+                 "intrinsics", "info", "unsorted_keys", "unsorted_payload", "tile_ids", "cell_masks")
 
     def sorted_keys(self) -> torch.Tensor:
         """The reference's sorted 64-bit keys (point_in_camera_sort_key, R.py:947) of this forward."""
@@ -321,7 +326,7 @@ def _check_inputs(pointcloud, features, invalid_mask, object_id, q, t, intrinsic
 
 def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
                   q_pointcloud_camera, t_pointcloud_camera, camera_info,
-                  keep_unsorted: bool = False) -> _ForwardState:
+                  keep_unsorted: bool = False, keep_cell_masks: bool = False) -> _ForwardState:
     dev = pointcloud.device
     intrinsics = camera_info.camera_intrinsics
     _check_inputs(pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
@@ -461,10 +466,14 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                                         st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
                                         stream), "gs_tile_ranges")
         _mark("tile_ranges")
+    # the forward's exact culling bits per (list entry, 8x4 cell), kept for the backward blend so that
+    # it does not redo the arithmetic: four planes (one per 8x8 quarter of a tile) of k bytes
+    st.cell_masks = torch.empty(4 * k, dtype=torch.uint8, device=dev) if (keep_cell_masks and REUSE_CELL_MASKS and k > 0) else None
     _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
                                   st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
-                                  st.last.data_ptr(), st.count.data_ptr(), int(rgb_only), stream),
+                                  st.last.data_ptr(), st.count.data_ptr(), int(rgb_only),
+                                  _ptr(st.cell_masks), k, stream),
                 "gs_blend_fwd")
     _mark("blend_fwd")
     st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
@@ -499,7 +508,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     _capi.check(_lib.gs_blend_bwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if st.k > 0 else None, buf.ptr("records"),
                                   g_img.data_ptr(), st.acc_alpha.data_ptr(), st.last.data_ptr(),
-                                  splat_grads.data_ptr(), _ptr(on_image), stream),
+                                  splat_grads.data_ptr(), _ptr(on_image), _ptr(st.cell_masks), st.k, stream),
                 "gs_blend_bwd")
     _mark("blend_bwd")
     h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None

@@ -102,13 +102,14 @@ __device__ __forceinline__ int reduced_slot(int lane)
     return 5 * (lane >> 4) + 3 * b3 + 2 * b2 + b1;
 }
 
-template <int kCells, bool kMagnitude>
+template <int kCells, bool kMagnitude, bool kMasks>
 __global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)))
 blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
                  const float4 *__restrict__ records, const float *__restrict__ image_grad,
                  const float *__restrict__ acc_alpha, const int32_t *__restrict__ last_effective,
-                 float *__restrict__ splat_grads, float *__restrict__ map_on_image)
+                 float *__restrict__ splat_grads, float *__restrict__ map_on_image,
+                 const uint8_t *__restrict__ cell_masks, const long long mask_stride)
 {
     constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile
     constexpr int kPartsPerColumn = kParts / 2;
@@ -169,9 +170,22 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             unsigned live = 0u;
 #pragma unroll
             for (int j = 0; j < kCells; ++j) live |= (my_i < cell_last[j] ? 1u : 0u) << j;
-            if (live)
-                my_mask = live & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z,
-                                                      x_first, y_first);  // (drops the irregular flag)
+            if (live) {
+                if (kMasks) {
+                    // the forward's culling bits for these cells: plane q = 2 * column + row half
+                    // of the tile's 8x8 quarters, two bits (upper / lower 8x4 cell) per entry
+                    unsigned m = 0u;
+#pragma unroll
+                    for (int h = 0; h < kCells / 2; ++h) {
+                        const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * (kCells / 2) + h;
+                        m |= ((unsigned)__ldg(cell_masks + q * mask_stride + my_i) & 3u) << (2 * h);
+                    }
+                    my_mask = live & m;
+                } else {
+                    my_mask = live & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z,
+                                                          x_first, y_first);  // (drops the irregular flag)
+                }
+            }
         }
         s_rec[3 * lane] = n0;
         s_rec[3 * lane + 1] = n1;
@@ -278,17 +292,19 @@ template <int kCells>
 int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t *tile_start,
                const int32_t *tile_end, const int32_t *payload, const float4 *rec,
                const float *image_grad, const float *acc_alpha, const int32_t *last_effective,
-               float *splat_grads, float *map_on_image)
+               float *splat_grads, float *map_on_image, const uint8_t *cell_masks, long long mask_stride)
 {
     constexpr int kThreads = 32 * (kTilePixels / (kCells * 32));
-    if (map_on_image)
-        blend_bwd_kernel<kCells, true><<<tiles, kThreads, 0, st>>>(
-            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,
-            splat_grads, map_on_image);
-    else
-        blend_bwd_kernel<kCells, false><<<tiles, kThreads, 0, st>>>(
-            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,
-            splat_grads, map_on_image);
+#define GS_BWD_LAUNCH(MAG, MSK)                                                                        \
+    blend_bwd_kernel<kCells, MAG, MSK><<<tiles, kThreads, 0, st>>>(                                     \
+        height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,      \
+        splat_grads, map_on_image, cell_masks, mask_stride)
+    if (map_on_image) {
+        if (cell_masks) GS_BWD_LAUNCH(true, true); else GS_BWD_LAUNCH(true, false);
+    } else {
+        if (cell_masks) GS_BWD_LAUNCH(false, true); else GS_BWD_LAUNCH(false, false);
+    }
+#undef GS_BWD_LAUNCH
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -299,8 +315,9 @@ extern "C" int gs_blend_bwd(int height, int width, const int32_t *tile_start,
                             const int32_t *tile_end, const int32_t *sorted_payload,
                             const float *records, const float *image_grad, const float *acc_alpha,
                             const int32_t *last_effective, float *splat_grads, float *map_on_image,
-                            void *stream)
+                            const uint8_t *cell_masks, int64_t mask_stride, void *stream)
 {
+    if (cell_masks && mask_stride < 0) return GS_E_INVALID;
     if (height <= 0 || width <= 0 || height % kTile || width % kTile) return GS_E_INVALID;
     if (!tile_start || !tile_end || !image_grad || !acc_alpha || !last_effective || !splat_grads)
         return GS_E_INVALID;
@@ -315,7 +332,9 @@ extern "C" int gs_blend_bwd(int height, int width, const int32_t *tile_start,
     cudaStream_t st = (cudaStream_t)stream;
     if (cells == 2)
         return launch_bwd<2>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
-                             image_grad, acc_alpha, last_effective, splat_grads, map_on_image);
+                             image_grad, acc_alpha, last_effective, splat_grads, map_on_image, cell_masks,
+                             mask_stride);
     return launch_bwd<4>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
-                         image_grad, acc_alpha, last_effective, splat_grads, map_on_image);
+                         image_grad, acc_alpha, last_effective, splat_grads, map_on_image, cell_masks,
+                         mask_stride);
 }

@@ -188,7 +188,8 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
                  const float4 *__restrict__ records, float *__restrict__ image,
                  float *__restrict__ depth, float *__restrict__ acc_alpha,
-                 int32_t *__restrict__ last_effective, int32_t *__restrict__ valid_count)
+                 int32_t *__restrict__ last_effective, int32_t *__restrict__ valid_count,
+                 uint8_t *__restrict__ cell_masks, const long long mask_stride)
 {
     constexpr int kParts = kTilePixels / (kPairs * 64);  // warps per tile
     constexpr int kPartsPerColumn = kParts / 2;
@@ -238,9 +239,24 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         // ---- stage this batch (registers -> shared) and cull it against the open pair cells -----
         unsigned my_mask = 0u;
         if (base + lane < end) {
-            unsigned raw = gs_cell_mask<kPairs, kPairH>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
+            // culling bits per 8x4 cell (two per pair cell); a pair cell is visited if either is set
+            unsigned fine =
+                gs_cell_mask<2 * kPairs, kCellH>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
             // non-finite colour / depth / opacity: the packed path's "add zero" is not a no-op
-            if (!isfinite(((n1.y + n1.z) + (n1.w + n2.x)) + (n2.y + n2.z))) raw = kAllPairs | kCellMaskIrregular;
+            if (!isfinite(((n1.y + n1.z) + (n1.w + n2.x)) + (n2.y + n2.z)))
+                fine = ((1u << (2 * kPairs)) - 1u) | kCellMaskIrregular;
+            unsigned raw = fine & kCellMaskIrregular;
+#pragma unroll
+            for (int c = 0; c < kPairs; ++c) raw |= ((fine >> (2 * c)) & 3u) ? (1u << c) : 0u;
+            // hand the bits to the backward blend (same cells, same entries): plane q of the tile's
+            // four 8x8 quarters, q = 2 * column + row half, one byte per list entry
+            if (cell_masks) {
+#pragma unroll
+                for (int c = 0; c < kPairs; ++c) {
+                    const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * kPairs + c;
+                    cell_masks[q * mask_stride + base + lane] = (uint8_t)((fine >> (2 * c)) & 3u);
+                }
+            }
             my_mask = (raw & open) ? (raw & (open | kCellMaskIrregular)) : 0u;
         }
         s_rec[3 * lane] = n0;
@@ -319,17 +335,17 @@ template <int kPairs>
 int launch_fwd(int tiles, cudaStream_t st, int rgb_only, int height, int width,
                const int32_t *tile_start, const int32_t *tile_end, const int32_t *payload,
                const float4 *rec, float *image, float *depth, float *acc_alpha,
-               int32_t *last_effective, int32_t *valid_count)
+               int32_t *last_effective, int32_t *valid_count, uint8_t *cell_masks, long long mask_stride)
 {
     constexpr int kThreads = 32 * (kTilePixels / (kPairs * 64));
     if (rgb_only)
         blend_fwd_kernel<kPairs, true><<<tiles, kThreads, 0, st>>>(
             height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
-            last_effective, valid_count);
+            last_effective, valid_count, cell_masks, mask_stride);
     else
         blend_fwd_kernel<kPairs, false><<<tiles, kThreads, 0, st>>>(
             height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
-            last_effective, valid_count);
+            last_effective, valid_count, cell_masks, mask_stride);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -340,8 +356,9 @@ extern "C" int gs_blend_fwd(int height, int width, const int32_t *tile_start,
                             const int32_t *tile_end, const int32_t *sorted_payload,
                             const float *records, float *image, float *depth, float *acc_alpha,
                             int32_t *last_effective, int32_t *valid_count, int rgb_only,
-                            void *stream)
+                            uint8_t *cell_masks, int64_t mask_stride, void *stream)
 {
+    if (cell_masks && mask_stride < 0) return GS_E_INVALID;
     if (height <= 0 || width <= 0 || height % kTile || width % kTile) return GS_E_INVALID;
     if (!tile_start || !tile_end || !image) return GS_E_INVALID;
     if (!rgb_only && (!depth || !acc_alpha || !last_effective || !valid_count)) return GS_E_INVALID;
@@ -356,7 +373,7 @@ extern "C" int gs_blend_fwd(int height, int width, const int32_t *tile_start,
     cudaStream_t st = (cudaStream_t)stream;
     if (pairs == 1)
         return launch_fwd<1>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload, rec,
-                             image, depth, acc_alpha, last_effective, valid_count);
+                             image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride);
     return launch_fwd<2>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload, rec,
-                         image, depth, acc_alpha, last_effective, valid_count);
+                         image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride);
 }

@@ -488,3 +488,31 @@ def test_view_sharded_step_on_two_lanes_matches_one_lane():
         for got, want in ((gx, results[0][0]), (gf, results[0][1])):
             l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
             assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
+
+
+def test_backward_with_and_without_the_forward_cell_masks():
+    """gs_blend_bwd either reads the culling bits gs_blend_fwd stored (default) or recomputes them;
+    both visit every contributing (pixel, entry) pair, so the gradients agree to rounding."""
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    scene = make_scene(30000, 256, 160, seed=27, scale_factor=0.015)
+    g = torch.from_numpy(np.random.default_rng(5).uniform(0, 1, (160, 256, 3)).astype(np.float32)).cuda()
+    grads = []
+    saved = impl.REUSE_CELL_MASKS
+    try:
+        for reuse in (True, False):
+            impl.REUSE_CELL_MASKS = reuse
+            hooked = {}
+            ras = _module(hook=lambda h: hooked.update(h=h))
+            t = util.scene_tensors(scene, requires_grad=True)
+            image, _, _ = _call(ras, scene, t, band=3)
+            (image * g).sum().backward()
+            grads.append((t["point_cloud"].grad.cpu().numpy(), t["point_cloud_features"].grad.cpu().numpy(),
+                          hooked["h"].num_affected_pixels.cpu().numpy(),
+                          hooked["h"].magnitude_grad_viewspace_on_image.cpu().numpy()))
+    finally:
+        impl.REUSE_CELL_MASKS = saved
+    assert np.array_equal(grads[0][2], grads[1][2])          # the same pairs were visited
+    for a, b in zip(grads[0][:2], grads[1][:2]):
+        l2, mx = util.grad_error(b, a)
+        assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
+    assert np.allclose(grads[0][3], grads[1][3], rtol=1e-4, atol=1e-7)
