@@ -64,15 +64,26 @@ __device__ __forceinline__ void load_halo_async(float *s, const float *src, cons
 {
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (st.c == 1) {
-        for (int r = warp; r < kHalo; r += kLossThreads / 32) {
-            const int y = y0 + r;
-            const bool row_ok = y < height;
-            const float *row = src + (row_ok ? y * st.h : 0);
+        // everything that depends on the position in the row is the same for every row: hoisted
+        int dst_off[4], src_off[4];
+        bool col_ok[4];
 #pragma unroll
-            for (int j = lane; j < 3 * kHalo; j += 32) {
-                const int col = j / 3, ch = j - col * 3;
-                const bool ok = row_ok && (x0 + col) < width;
-                cp_async4(s + (ch * kHalo + r) * kInStride + col, ok ? row + (x0 + col) * st.w + ch : src, ok);
+        for (int t = 0; t < 4; ++t) {
+            const int j = lane + 32 * t, col = j / 3, ch = j - col * 3;
+            col_ok[t] = j < 3 * kHalo && (x0 + col) < width;
+            dst_off[t] = ch * kHalo * kInStride + col;
+            src_off[t] = (int)((x0 + col) * st.w) + ch;
+        }
+        for (int r = warp; r < kHalo; r += kLossThreads / 32) {
+            const bool row_ok = (y0 + r) < height;
+            const float *row = src + (row_ok ? (y0 + r) * st.h : 0);
+            float *drow = s + r * kInStride;
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                if (lane + 32 * t < 3 * kHalo) {
+                    const bool ok = row_ok && col_ok[t];
+                    cp_async4(drow + dst_off[t], ok ? row + src_off[t] : src, ok);
+                }
             }
         }
     } else {
@@ -133,13 +144,18 @@ loss_fwd_kernel(const float *__restrict__ image, const Strides ist, const float 
     {
         const int own_h = (blockIdx.y == gridDim.y - 1) ? min(kHalo, height - y0) : kLossTile;
         const int own_w = (blockIdx.x == gridDim.x - 1) ? min(kHalo, width - x0) : kLossTile;
-        for (int i = threadIdx.x; i < 3 * kHalo * kInStride; i += kLossThreads) {
-            const int cr = i / kInStride, col = i - cr * kInStride;
-            const int r = cr % kHalo;
-            if (col >= kHalo) continue;  // padding column
-            const float x = clamp01(sx[i]);
-            sx[i] = x;
-            if (r < own_h && col < own_w) l1 += fabsf(x - sy[i]);
+        const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            for (int r = warp; r < kHalo; r += kLossThreads / 32) {
+#pragma unroll
+                for (int col = lane; col < kHalo; col += 32) {
+                    const int i = (ch * kHalo + r) * kInStride + col;
+                    const float x = clamp01(sx[i]);
+                    sx[i] = x;
+                    if (r < own_h && col < own_w) l1 += fabsf(x - sy[i]);
+                }
+            }
         }
     }
     __syncthreads();
@@ -209,7 +225,7 @@ loss_fwd_kernel(const float *__restrict__ image, const Strides ist, const float 
                 const float s1 = f[2][o] - mu1 * mu1, s2 = f[3][o] - mu2 * mu2, s12 = f[4][o] - mu1 * mu2;
                 const float a1 = 2.0f * mu1 * mu2 + kC1, a2 = 2.0f * s12 + kC2;
                 const float b1 = mu1 * mu1 + mu2 * mu2 + kC1, b2 = s1 + s2 + kC2;
-                const float rb1 = 1.0f / b1, rb2 = 1.0f / b2;
+                const float rb1 = __frcp_rn(b1), rb2 = __frcp_rn(b2);
                 const float lum = a1 * rb1, cs = a2 * rb2;
                 ssim_sum += lum * cs;
                 const float d_s1 = -(lum * cs) * rb2;
@@ -344,22 +360,37 @@ loss_bwd_kernel(const float *__restrict__ image, const Strides ist, const float 
     for (int k = 0; k < kWin; ++k) w[k] = c_win[k];
 
     const int vc = threadIdx.x & 31, vg = threadIdx.x >> 5;
-    for (int ch = 0; ch < 3; ++ch) {
-        // halo of the three maps: map positions (y0-10 .. y0+31, x0-10 .. x0+31), zero outside;
-        // one warp per row, all copies in flight at once
+    // halo of the three maps of one channel: map positions (y0-10 .. y0+31, x0-10 .. x0+31), zero
+    // outside; one warp per row, all copies in flight at once; the column part is row-invariant
+    int mcol[2];
+    bool mcol_ok[2];
+#pragma unroll
+    for (int t = 0; t < 2; ++t) {
+        const int col = (threadIdx.x & 31) + 32 * t;
+        mcol[t] = x0 - (kWin - 1) + col;
+        mcol_ok[t] = col < kHalo && mcol[t] >= 0 && mcol[t] < ow;
+    }
+    auto issue_maps = [&](const int ch, float *dst) {
         for (int qr = threadIdx.x >> 5; qr < 3 * kHalo; qr += kLossThreads / 32) {
             const int q = qr / kHalo, r = qr - q * kHalo;
             const int my = y0 - (kWin - 1) + r;
             const bool row_ok = my >= 0 && my < oh;
             const float *row = maps + (q * 3 + ch) * plane + (row_ok ? (size_t)my * ow : 0);
 #pragma unroll
-            for (int col = threadIdx.x & 31; col < kHalo; col += 32) {
-                const int mx = x0 - (kWin - 1) + col;
-                const bool ok = row_ok && mx >= 0 && mx < ow;
-                cp_async4(sin + qr * kInStride + col, ok ? row + mx : maps, ok);
+            for (int t = 0; t < 2; ++t) {
+                if ((int)(threadIdx.x & 31) + 32 * t < kHalo) {
+                    const bool ok = row_ok && mcol_ok[t];
+                    cp_async4(dst + qr * kInStride + (threadIdx.x & 31) + 32 * t, ok ? row + mcol[t] : maps, ok);
+                }
             }
         }
-        cp_async_wait_all();
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    for (int ch = 0; ch < 3; ++ch) {
+        // (a second buffer to prefetch the next channel costs a resident block per SM: measured slower)
+        const float *cur = sin;
+        issue_maps(ch, sin);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
         __syncthreads();
         // horizontal: out(x) = sum_k w[k] * m(x - k); halo column of m(x - k) is (x - x0) + 10 - k
         for (int task = threadIdx.x; task < kHalo * (kLossTile / 4); task += kLossThreads) {
@@ -367,7 +398,7 @@ loss_bwd_kernel(const float *__restrict__ image, const Strides ist, const float 
             float a[3][4];
 #pragma unroll
             for (int q = 0; q < 3; ++q) {
-                const float *pm = sin + (q * kHalo + r) * kInStride + 4 * g;
+                const float *pm = cur + (q * kHalo + r) * kInStride + 4 * g;
 #pragma unroll
                 for (int o = 0; o < 4; ++o) a[q][o] = 0.0f;
 #pragma unroll
