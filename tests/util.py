@@ -45,6 +45,21 @@ def literal_unsorted_keys(st, width):
     return keys[:st.k], pay[:st.k]
 
 
+def cuda_forward_state(scene, near=0.8, far=1000.0, scale=100.0):
+    """The operator's forward state with every buffer left on the device (large cases)."""
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    t = scene_tensors(scene)
+    cfg = impl.GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig(
+        near_plane=near, far_plane=far, depth_to_sort_key_scale=scale)
+    cam = CameraInfo(camera_intrinsics=t["camera_intrinsics"], camera_height=scene.height,
+                     camera_width=scene.width, camera_id=0)
+    st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"], t["point_invalid_mask"],
+                            t["point_object_id"], t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam)
+    torch.cuda.synchronize()
+    return st
+
+
 def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False, pipeline=None):
     """Run the product forward through its C ABI and return every stage as numpy arrays.
     pipeline: None (the module default), "depth_first" or "literal"."""
