@@ -164,3 +164,33 @@ def test_invalid_arguments():
         _module()(torch.zeros(2, 3, 16, 16, device=dev), torch.zeros(2, 3, 16, 16, device=dev))
     with pytest.raises(ValueError):
         _module()(torch.zeros(3, 16, 16), torch.zeros(3, 16, 16))
+
+
+def test_folded_regulariser_gradient_matches_the_autograd_one():
+    """LossFunction(fold_regulariser_gradient=True): the regulariser's gradient is added in place to
+    the gradient arriving at the features from another consumer (here a stand-in for the rasteriser)
+    instead of travelling as a second dense tensor; same totals, upstream scale included."""
+    img, gt = _images(32, 48, 31)
+    rng = np.random.default_rng(32)
+    n = 4000
+    feat = rng.normal(0, 1, (n, 56)).astype(np.float32)
+    mask = (rng.uniform(size=n) < 0.1).astype(np.int8)
+    wmat = rng.normal(0, 1, (n, 56)).astype(np.float32)
+    dev = torch.device("cuda")
+    results = []
+    for fold in (False, True):
+        from taichi_3d_gaussian_splatting_b200.LossFunction import LossFunction
+        lf = LossFunction(LossFunction.LossFunctionConfig(), fold_regulariser_gradient=fold)
+        t_img = torch.from_numpy(img).to(dev).requires_grad_(True)
+        t_feat = torch.from_numpy(feat).to(dev).requires_grad_(True)
+        other = (t_feat * torch.from_numpy(wmat).to(dev)).sum() * 1e-3      # the "rasteriser" path
+        loss, _, _ = lf.forward_rasterised(t_img, torch.from_numpy(gt).to(dev), torch.from_numpy(mask).to(dev), t_feat)
+        (2.5 * (loss + other)).backward()
+        results.append((loss.item(), t_feat.grad.cpu().numpy(), t_img.grad.cpu().numpy()))
+    assert results[0][0] == results[1][0]
+    assert np.allclose(results[0][1], results[1][1], rtol=1e-6, atol=1e-9)
+    assert np.array_equal(results[0][2], results[1][2])
+    o = LO.total_loss(img, gt, feat, mask, 0.2, True, 2.0)
+    want = 2.5 * (1e-3 * wmat.astype(np.float64))
+    want[:, 4:7] += 2.5 * o["grad_scale"]
+    assert np.allclose(results[1][1], want, rtol=2e-5, atol=1e-8)

@@ -35,6 +35,7 @@ def main():
     ap.add_argument("--steps", type=int, default=30)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--workload", default="c2_1m_1920x1088", choices=list(bench.WORKLOADS))
+    ap.add_argument("--arms", default="fused,torch")
     args = ap.parse_args()
     n, w, h, sf, seed = bench.WORKLOADS[args.workload]
     dev = torch.device("cuda:0")
@@ -47,14 +48,14 @@ def main():
     win = torch.tensor(WINDOW, device=dev).repeat(3, 1, 1, 1)
     out = {"what": "training iteration", "workload": args.workload, "steps": args.steps}
 
-    for arm in ("fused", "torch"):
+    for arm in args.arms.split(","):
         xyz = torch.nn.Parameter(t(scene.point_cloud))
         feat = torch.nn.Parameter(t(scene.point_cloud_features))
         if arm == "fused":
             acc = AdaptiveControllerAccumulators(n, dev)
             hook = acc.update
             o_feat, o_xyz = FusedAdam([feat], lr=5e-3), FusedAdam([xyz], lr=1e-5)
-            lf = LossFunction(LossFunction.LossFunctionConfig())
+            lf = LossFunction(LossFunction.LossFunctionConfig(), fold_regulariser_gradient=True)
         else:
             stats = {k: torch.zeros(n, device=dev) for k in "abcd"}
             stats["p"] = torch.zeros(n, 3, device=dev)
@@ -117,7 +118,8 @@ def main():
         out[f"{arm}_loss"] = float(last)
         del xyz, feat, o_feat, o_xyz, ras
         torch.cuda.empty_cache()
-    out["speedup"] = round(out["torch_ms_per_iteration"] / out["fused_ms_per_iteration"], 2)
+    if "torch_ms_per_iteration" in out and "fused_ms_per_iteration" in out:
+        out["speedup"] = round(out["torch_ms_per_iteration"] / out["fused_ms_per_iteration"], 2)
     print(json.dumps(out))
 
 
