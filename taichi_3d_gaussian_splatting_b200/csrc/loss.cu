@@ -264,9 +264,11 @@ scale_reg_fwd_kernel(const float *__restrict__ features, const int8_t *__restric
     float sum = 0.0f, cnt = 0.0f;
     for (long long i = (long long)blockIdx.x * kRegThreads + threadIdx.x; i < n;
          i += (long long)gridDim.x * kRegThreads) {
-        if (invalid_mask[i] != 0) continue;
+        // the row is fetched whether or not the point is valid: the loads are independent of the mask
         const float *row = features + i * 56 + 4;
-        const float e0 = expf(row[0]), e1 = expf(row[1]), e2 = expf(row[2]);
+        const float s0 = __ldg(row), s1 = __ldg(row + 1), s2 = __ldg(row + 2);
+        if (invalid_mask[i] != 0) continue;
+        const float e0 = expf(s0), e1 = expf(s1), e2 = expf(s2);
         sum += sqrtf(e0 * e0 + e1 * e1 + e2 * e2);
         cnt += 1.0f;
     }
