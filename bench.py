@@ -135,7 +135,15 @@ class ClockSampler:
 def stage_bytes(n, m, k, tiles, hw, info):
     """ALGORITHMIC bytes per call of each stage (stated in DESIGN.md)."""
     depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
-    if info.get("key_pipeline") == "depth_first":
+    if info.get("key_pipeline") == "binned":
+        pm = (depth_bits + 7) // 8
+        keys = {
+            "sort_points": m * (4 + 16 * pm - 4),
+            # order + bbox in, payload + ranges out (the 8-byte column entries in between are the
+            # implementation's, not the algorithm's)
+            "bin_tiles": 12 * m + 4 * k + 8 * tiles,
+        }
+    elif info.get("key_pipeline") == "depth_first":
         pm, pk = (depth_bits + 7) // 8, (tile_bits + 7) // 8
         keys = {
             # argsort of M 4-byte depth keys: histogram read + per pass key/value read and write
@@ -498,7 +506,11 @@ def run_b200(args):
                             alt_frac=d["fp32_frac"])
 
     depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
-    if info.get("key_pipeline") == "depth_first":
+    if info.get("key_pipeline") == "binned":
+        # pose, project | point sort: hist+scan+passes | bin: count, columns, rows, ranges |
+        # blend_fwd, blend_bwd, point_bwd   (memsets are not counted)
+        launches_per_step = 2 + (2 + (depth_bits + 7) // 8) + 4 + 3
+    elif info.get("key_pipeline") == "depth_first":
         # pose, project | point sort: hist+scan+passes | emit | pair sort: hist+scan+passes |
         # ranges, blend_fwd, blend_bwd, point_bwd
         launches_per_step = 2 + (2 + (depth_bits + 7) // 8) + 1 + (2 + (tile_bits + 7) // 8) + 4

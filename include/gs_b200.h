@@ -132,6 +132,25 @@ int gs_sorted_keys(const uint32_t *sorted_tile_ids, const int32_t *sorted_payloa
                    const int32_t *depth_key, int64_t k, int64_t *keys, void *stream);
 
 /*
+ * Tile-binned key pipeline (the default product path for images up to 4096 x 4096 and depth keys
+ * that fit 31 bits).  After gs_sort_points_by_depth, ONE call replaces
+ * generate_point_sort_key_by_num_overlap_tiles (R.py:131-172), Tensor.sort() + gather
+ * (R.py:947-950) and find_tile_start_and_end (R.py:175-193): the depth-ordered points are split,
+ * stably, first over the tile columns and then over the tile rows they cover, so that no (key,
+ * payload) pair per list entry is ever written or sorted.  payload [k] i32, tile_start / tile_end
+ * [tiles] i32 are bit-identical to those of the pair-sort chain above (and so to a stable sort of the
+ * reference's 64-bit keys); empty tiles read (0, 0) as in the reference.
+ *   entries: scratch, gs_bin_entries_capacity(m, k, width) x 8 bytes; workspace:
+ *   gs_bin_workspace_bytes.  GS_E_CAPACITY if the image has more than 256 tile columns or rows
+ *   or k >= 2^30 (callers then use the pair-sort chain).
+ */
+int64_t gs_bin_workspace_bytes(int64_t m, int64_t k, int width, int height);
+int64_t gs_bin_entries_capacity(int64_t m, int64_t k, int width);
+int gs_bin_tiles(const int32_t *order, const uint16_t *bbox, int64_t m, int64_t k, int width, int height,
+                 uint64_t *entries, int32_t *payload, int32_t *tile_start, int32_t *tile_end,
+                 void *workspace, void *stream);
+
+/*
  * Tile ranges.  Replaces find_tile_start_and_end (R.py:175-193).  start/end [num_tiles] i32
  * are zeroed by this call (R.py:954-957) and then filled.
  */

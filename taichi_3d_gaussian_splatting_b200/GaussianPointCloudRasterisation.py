@@ -42,7 +42,10 @@ _GRAD_SLOTS = 12
 # "depth_first": sort the points by depth, emit tile ids in that order, sort by tile id only (a third
 # of the sort traffic; same payload order and tile ranges).  "literal": build and sort the reference's
 # 64-bit keys (R.py:131-172, 947-950); also taken automatically when depth keys can be negative.
-KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "depth_first")
+# "binned": after the same point sort, split the points over tile columns and then tile rows
+# (gs_bin_tiles): no (tile id, payload) pair per list entry is written or sorted; same payload order and
+# tile ranges.  Falls back to "depth_first" when the image has more than 256 tile columns or rows.
+KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "binned")
 
 # the backward blend reuses the culling bits the forward blend computed (4 bytes per list entry kept
 # between forward and backward); 0 makes it recompute them
@@ -296,6 +299,11 @@ class _ForwardState:
         if self.keys is not None:
             return self.keys
         keys = torch.empty(self.k, dtype=torch.int64, device=self.payload.device)
+        if self.k > 0 and self.tile_ids is None:
+            # binned pipeline: the lists are contiguous in tile order, so the ids follow from the ranges
+            lengths = (self.tile_end - self.tile_start).to(torch.int64)
+            self.tile_ids = torch.repeat_interleave(
+                torch.arange(lengths.numel(), dtype=torch.int32, device=lengths.device), lengths)
         if self.k > 0:
             stream = torch.cuda.current_stream(keys.device).cuda_stream
             _capi.check(_lib.gs_sorted_keys(self.tile_ids.data_ptr(), self.payload.data_ptr(),
@@ -372,7 +380,9 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
     depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
                                           float(cfg.depth_to_sort_key_scale), num_tiles)
-    depth_first = KEY_PIPELINE == "depth_first" and depth_bits <= 31
+    depth_first = KEY_PIPELINE in ("depth_first", "binned") and depth_bits <= 31
+    binned = (depth_first and KEY_PIPELINE == "binned" and W // TILE_WIDTH <= 256
+              and H // TILE_HEIGHT <= 256)
     order = None
     if depth_first and n > 0:
         # The argsort of the visible points by depth needs M only on the device: enqueue it for
@@ -405,7 +415,21 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
 
     kk = max(k, 1)
     st.tile_ids = None
-    if depth_first:
+    if binned and k < (1 << 30):
+        # points sorted by depth -> split over tile columns -> split over tile rows
+        st.keys = None
+        st.payload = torch.empty(kk, dtype=torch.int32, device=dev)[:k]
+        if k > 0:
+            entries = torch.empty(int(_lib.gs_bin_entries_capacity(m, k, W)), dtype=torch.int64, device=dev)
+            bin_ws = torch.empty(int(_lib.gs_bin_workspace_bytes(m, k, W, H)), dtype=torch.uint8, device=dev)
+        _mark("host_sync_and_alloc")
+        _capi.check(_lib.gs_bin_tiles(order.data_ptr() if k > 0 else None, buf.ptr("bbox"), m, k, W, H,
+                                      entries.data_ptr() if k > 0 else None,
+                                      st.payload.data_ptr() if k > 0 else None,
+                                      st.tile_start.data_ptr(), st.tile_end.data_ptr(),
+                                      bin_ws.data_ptr() if k > 0 else None, stream), "gs_bin_tiles")
+        _mark("bin_tiles")
+    elif depth_first:
         # points sorted by depth -> tile ids emitted in that order -> stable sort by tile id only
         tid2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
         pay2 = torch.empty(2 * kk, dtype=torch.int32, device=dev)
@@ -477,7 +501,8 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                 "gs_blend_fwd")
     _mark("blend_fwd")
     st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
-                   tile_bits=tile_bits, key_pipeline="depth_first" if depth_first else "literal")
+                   tile_bits=tile_bits,
+                   key_pipeline=("binned" if binned else "depth_first") if depth_first else "literal")
     return st
 
 

@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
 
-ABI_VERSION = 107
+ABI_VERSION = 108
 
 _p = C.c_void_p
 _i = C.c_int
@@ -34,6 +34,9 @@ SIGNATURES = {
     "gs_sort_pairs32": (_i, [_p, _p, _p, _p, _l, _i, _p, _p, C.POINTER(C.c_int), _p]),
     "gs_tile_ranges32": (_i, [_p, _l, _p, _p, _i, _p]),
     "gs_sorted_keys": (_i, [_p, _p, _p, _l, _p, _p]),
+    "gs_bin_workspace_bytes": (_l, [_l, _l, _i, _i]),
+    "gs_bin_entries_capacity": (_l, [_l, _l, _i]),
+    "gs_bin_tiles": (_i, [_p, _p, _l, _l, _i, _i, _p, _p, _p, _p, _p, _p]),
     "gs_inverse_pose": (_i, [_p, _p, _i, _p, _p, _p]),
     "gs_project_cull_sh": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
                                 _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

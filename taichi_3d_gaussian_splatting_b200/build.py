@@ -24,6 +24,7 @@ UNITS = {
     "project.cu": ["-fmad=false"],
     "keys.cu": [],
     "sort.cu": [],
+    "bin.cu": [],
     "blend_fwd.cu": ["-fmad=false"],
     "blend_bwd.cu": [],
     "point_bwd.cu": [],

@@ -193,6 +193,80 @@ def test_emit_tile_keys_follows_the_given_order():
     assert np.array_equal(s_np[nz], (np.cumsum(counts) - counts)[nz]) and not s_np[~nz].any()
 
 
+def _bin_tiles_case(W, H, m, rng, wide_every=13, empty_every=7, max_span=6):
+    tw, th = W // 16, H // 16
+    tu0 = rng.integers(0, tw + 1, m); tu1 = np.minimum(tu0 + rng.integers(0, max_span, m), tw)
+    tv0 = rng.integers(0, th + 1, m); tv1 = np.minimum(tv0 + rng.integers(0, max_span, m), th)
+    if wide_every:
+        tu0[::wide_every], tu1[::wide_every], tv0[::wide_every], tv1[::wide_every] = 0, tw, 0, th
+    if empty_every:
+        tu1[3::empty_every] = tu0[3::empty_every]
+    return np.stack([tu0, tu1, tv0, tv1], 1).astype(np.uint16)
+
+
+@pytest.mark.parametrize("shape", [(320, 208, 3000), (16, 16, 5000), (4096, 16, 2500), (16, 4096, 2500),
+                                   (1920, 1088, 200000), (64, 48, 1), (976, 544, 1023), (976, 544, 1025)])
+def test_bin_tiles_equals_stable_sort_by_tile_id(shape):
+    """gs_bin_tiles (column split, then row split of the depth-ordered points) gives the payload order
+    and the tile ranges of a stable sort of the emitted (tile id, payload) pairs by tile id -- the
+    order R.py:947-950 produces with stable ties -- including whole-image, empty and clipped boxes."""
+    capi = _lib()
+    W, H, m = shape
+    tw, th = W // 16, H // 16
+    rng = np.random.default_rng(W * 31 + H + m)
+    bbox = _bin_tiles_case(W, H, m, rng, wide_every=13 if m <= 5000 else 997,
+                           max_span=6 if m <= 5000 else 4)
+    order_np = rng.permutation(m).astype(np.int32)
+    b = bbox[order_np].astype(np.int64)
+    wdt, hgt = np.maximum(b[:, 1] - b[:, 0], 0), np.maximum(b[:, 3] - b[:, 2], 0)
+    cnt = wdt * hgt
+    k = int(cnt.sum())
+    rep = np.repeat(np.arange(m), cnt)
+    within = np.arange(k) - np.repeat(np.cumsum(cnt) - cnt, cnt)
+    hh = np.maximum(hgt[rep], 1)
+    ids_ref = (b[rep, 0] + within // hh) + (b[rep, 2] + within % hh) * tw   # emission order of R.py:161-172
+    pay_ref = order_np[rep]
+    srt = np.argsort(ids_ref, kind="stable")
+    want_pay = pay_ref[srt]
+    counts = np.bincount(ids_ref, minlength=tw * th)
+    dev = torch.device("cuda")
+    d_bbox = torch.from_numpy(bbox.view(np.int16)).to(dev)
+    d_order = torch.from_numpy(order_np).to(dev)
+    cap = int(capi.lib.gs_bin_entries_capacity(m, k, W))
+    assert cap == min(k, m * tw)
+    entries = torch.empty(max(cap, 1), dtype=torch.int64, device=dev)
+    pay = torch.full((max(k, 1),), -7, dtype=torch.int32, device=dev)
+    ws = torch.empty(int(capi.lib.gs_bin_workspace_bytes(m, k, W, H)), dtype=torch.uint8, device=dev)
+    start = torch.full((tw * th,), -1, dtype=torch.int32, device=dev)
+    end = torch.full((tw * th,), -1, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    for _ in range(2):   # the workspace is reusable without clearing by the caller
+        capi.check(capi.lib.gs_bin_tiles(d_order.data_ptr(), d_bbox.data_ptr(), m, k, W, H, entries.data_ptr(),
+                                         pay.data_ptr(), start.data_ptr(), end.data_ptr(), ws.data_ptr(), st),
+                   "gs_bin_tiles")
+        torch.cuda.synchronize()
+        assert np.array_equal(pay[:k].cpu().numpy(), want_pay)
+        s_np, e_np = start.cpu().numpy(), end.cpu().numpy()
+        assert np.array_equal(e_np - s_np, counts)
+        nz = counts > 0
+        assert np.array_equal(s_np[nz], (np.cumsum(counts) - counts)[nz]) and not s_np[~nz].any()
+
+
+def test_bin_tiles_empty_and_capacity():
+    capi = _lib()
+    dev = torch.device("cuda")
+    start = torch.full((12,), -1, dtype=torch.int32, device=dev)
+    end = torch.full((12,), -1, dtype=torch.int32, device=dev)
+    st = torch.cuda.current_stream().cuda_stream
+    capi.check(capi.lib.gs_bin_tiles(None, None, 0, 0, 64, 48, None, None, start.data_ptr(), end.data_ptr(),
+                                     None, st), "gs_bin_tiles")
+    torch.cuda.synchronize()
+    assert not start.any() and not end.any()
+    assert capi.lib.gs_bin_tiles(None, None, 0, 0, 16 * 257, 16, None, None, start.data_ptr(),
+                                 end.data_ptr(), None, st) == -2  # GS_E_CAPACITY
+    assert capi.lib.gs_bin_workspace_bytes(10, 10, 16 * 257, 16) == -2  # GS_E_CAPACITY
+
+
 def test_tile_ranges_reference_golden_vector():
     """tests/GaussianPointCloudRasterisation_test.py:18-51 of the reference, same call."""
     from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import find_tile_start_and_end

@@ -28,8 +28,8 @@ SCENES = {
 }
 
 
-# both key pipelines must give the reference's sorted keys, payload order and tile ranges
-CASES = [(name, "depth_first") for name in SCENES] + \
+# all three key pipelines must give the reference's sorted keys, payload order and tile ranges
+CASES = [(name, "depth_first") for name in SCENES] + [(name, "binned") for name in SCENES] + \
         [(name, "literal") for name in ("c1_1k_64x64", "dense_deep_lists_32x32", "truck_cfg_100k_976x544")]
 
 

@@ -66,7 +66,7 @@ def test_oracle_reproduces_the_reference_source(path, oracle32):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("pipeline", ["depth_first", "literal"])
+@pytest.mark.parametrize("pipeline", ["depth_first", "binned", "literal"])
 @pytest.mark.parametrize("path", GOLDEN, ids=[os.path.basename(p)[:-4] for p in GOLDEN])
 def test_cuda_path_reproduces_the_reference_source(path, pipeline):
     import torch

@@ -62,7 +62,7 @@ def cuda_forward_state(scene, near=0.8, far=1000.0, scale=100.0):
 
 def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False, pipeline=None):
     """Run the product forward through its C ABI and return every stage as numpy arrays.
-    pipeline: None (the module default), "depth_first" or "literal"."""
+    pipeline: None (the module default), "binned", "depth_first" or "literal"."""
     from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
     import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
     from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
