@@ -57,6 +57,12 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2_1m_1920x1088", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--timeline", default=None,
+                    help="also write the kernel timeline (name, stream, start, duration; CUPTI through "
+                         "torch.profiler) of two untimed resident steps to this JSON file")
+    ap.add_argument("--priority-sections", type=int, default=0,
+                    help="with lanes > 1: the small kernels of a view (projection, sorts, binning, per-point "
+                         "backward) run on a high-priority companion stream of the lane")
     ap.add_argument("--lanes", type=int, default=4,
                     help="CUDA streams the views of a step are spread over (view j on lane j mod L)")
     return ap.parse_args()
@@ -431,9 +437,12 @@ def run_b200(args):
     warmup = max(args.warmup, 3)
     sampler = ClockSampler(local_rank)
     prof = StageProfiler()
+    prio = bool(args.priority_sections) and lanes > 1
+    impl.PRIORITY_SECTIONS = prio
     timed(step_resident, 0, warmup)            # untimed warm-up (allocator, module load)
     sampler.start()
     ms_resident = timed(step_resident, args.steps, 0)
+    impl.PRIORITY_SECTIONS = False
     # per-stage CUDA-event times (stages, roofline): the same steps once more on ONE stream, because
     # events bracket a stage only when nothing else is in flight (all ranks run it: all-reduce inside)
     stage_steps = min(args.steps, 10)
@@ -442,9 +451,22 @@ def run_b200(args):
     ms_single_stream = timed(step_resident_single_stream, stage_steps, 0)
     stage_ms = prof.summary() if rank == 0 else {}
     impl.STAGE_PROFILER = None
+    impl.PRIORITY_SECTIONS = prio
     ms_e2e = timed(step_e2e, args.steps, warmup)
+    impl.PRIORITY_SECTIONS = False
     ms_render = timed(step_render, args.steps, warmup)
     clocks = sampler.stop()
+    if args.timeline and rank == 0:
+        from torch.profiler import ProfilerActivity, profile
+        impl.PRIORITY_SECTIONS = prio
+        step_resident(0)
+        torch.cuda.synchronize()
+        with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tl:
+            step_resident(1)
+            step_resident(2)
+            torch.cuda.synchronize()
+        impl.PRIORITY_SECTIONS = False
+        tl.export_chrome_trace(args.timeline)
 
     info = ras.last_forward_info
     m, k = int(info["num_points_in_camera"]), int(info["num_keys"])
@@ -529,7 +551,7 @@ def run_b200(args):
                    "step": f"{VIEWS_PER_RANK} views forward+backward per rank, gradients summed in "
                            "place, one all-reduce; an iteration (it) = one view forward+backward",
                    "views_per_rank_per_step": VIEWS_PER_RANK,
-                   "lanes": lanes,
+                   "lanes": lanes, "priority_sections": prio,
                    "lanes_note": f"view j of a step runs on CUDA stream j mod {lanes}; `stages` / `roofline` are "
                                  f"timed in a separate single-stream pass of {stage_steps} steps "
                                  f"({ms_single_stream / stage_steps:.3f} ms per step there)",

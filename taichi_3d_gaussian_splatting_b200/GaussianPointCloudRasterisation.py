@@ -54,6 +54,33 @@ REUSE_CELL_MASKS = os.environ.get("GS_REUSE_CELL_MASKS", "1") != "0"
 # set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
 STAGE_PROFILER = None
 
+# Priority sections.  The two blend kernels fill every SM's register file and are bound by instruction
+# issue; the kernels around them (projection, point sort, binning, per-point backward) are latency /
+# HBM bound.  When several views are in flight on different streams, the CTAs of a small kernel would
+# wait behind the thousands of queued CTAs of another view's blend kernel.  With this switch the small
+# kernels of a view run on a HIGH-PRIORITY companion of the caller's stream (chained to it by events, so
+# the order of a view's kernels is unchanged): their CTAs are dispatched as soon as blend CTAs retire
+# and run in the issue slots the blend kernels leave idle.  Off by default: a single view on a single
+# stream gains nothing and pays four event hand-offs.
+PRIORITY_SECTIONS = os.environ.get("GS_PRIORITY_SECTIONS", "0") != "0"
+_COMPANION = {}
+
+
+def _companion_stream(cur: "torch.cuda.Stream") -> "torch.cuda.Stream":
+    key = (cur.device.index, cur.cuda_stream)
+    s = _COMPANION.get(key)
+    if s is None:
+        s = _COMPANION[key] = torch.cuda.Stream(cur.device, priority=-1)
+    return s
+
+
+def _hand_over(src: "torch.cuda.Stream", dst: "torch.cuda.Stream") -> None:
+    """Work enqueued on dst from here on runs after everything enqueued on src so far."""
+    if src is not dst:
+        ev = torch.cuda.Event()
+        ev.record(src)
+        dst.wait_event(ev)
+
 
 def _mark(name: str) -> None:
     if STAGE_PROFILER is not None:
@@ -351,7 +378,10 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     Kmat = intrinsics.detach().to(device=dev, dtype=torch.float32).contiguous()
     q_pc = q_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
     t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
-    stream = torch.cuda.current_stream(dev).cuda_stream
+    s_big = torch.cuda.current_stream(dev)
+    s_small = _companion_stream(s_big) if PRIORITY_SECTIONS else s_big
+    _hand_over(s_big, s_small)
+    stream = s_small.cuda_stream  # everything up to the tile lists; the blend runs on s_big
 
     st = _ForwardState()
     st.n, st.width, st.height, st.intrinsics = n, W, H, Kmat
@@ -376,7 +406,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
     _mark("project_cull_sh")
     after_project = torch.cuda.Event()
-    after_project.record(torch.cuda.current_stream(dev))
+    after_project.record(s_small)
     num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
     depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
                                           float(cfg.depth_to_sort_key_scale), num_tiles)
@@ -493,6 +523,8 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     # the forward's exact culling bits per (list entry, 8x4 cell), kept for the backward blend so that
     # it does not redo the arithmetic: four planes (one per 8x8 quarter of a tile) of k bytes
     st.cell_masks = torch.empty(4 * k, dtype=torch.uint8, device=dev) if (keep_cell_masks and REUSE_CELL_MASKS and k > 0) else None
+    _hand_over(s_small, s_big)
+    stream = s_big.cuda_stream
     _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
                                   st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
@@ -511,7 +543,9 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
                    hook, hook_input_type, accumulate_into=None):
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
-    stream = torch.cuda.current_stream(dev).cuda_stream
+    s_big = torch.cuda.current_stream(dev)
+    s_small = _companion_stream(s_big) if PRIORITY_SECTIONS else s_big
+    stream = s_big.cuda_stream
     _mark("backward_begin")
     if accumulate_into is not None:
         grad_pointcloud, grad_features = accumulate_into
@@ -543,6 +577,8 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     h_aff = torch.empty(m, dtype=torch.int32, device=dev) if want_hook else None
     t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
     if m > 0:
+        _hand_over(s_big, s_small)
+        stream = s_small.cuda_stream
         _capi.check(_lib.gs_point_bwd(
             pointcloud.detach().contiguous().data_ptr(), pointcloud_features.detach().data_ptr(),
             point_object_id.contiguous().data_ptr(), st.intrinsics.data_ptr(), st.q_cam.data_ptr(),
@@ -553,6 +589,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
             grad_pointcloud.data_ptr(), grad_features.data_ptr(), _ptr(h_xyz), _ptr(h_feat),
             _ptr(h_view), _ptr(h_mag), _ptr(h_aff), int(accumulate_into is not None), stream),
             "gs_point_bwd")
+        _hand_over(s_small, s_big)
     _mark("point_bwd")
     if want_hook:
         point_in_camera = buf.view("point_in_camera", m)

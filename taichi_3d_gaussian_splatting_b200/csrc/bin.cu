@@ -35,29 +35,11 @@ constexpr uint32_t kBinAggregate = 1u << 30;
 constexpr uint32_t kBinPrefix = 2u << 30;
 constexpr uint32_t kBinValue = (1u << 30) - 1;
 
-// workspace, in 32-bit words
-constexpr int kWsColHist = 0, kWsRowHist = kMaxBins, kWsTickets = 2 * kMaxBins, kWsHeader = 2 * kMaxBins + 8;
-
-// per-column entry counts and per-row list lengths of the M visible points (any order)
-__global__ void __launch_bounds__(256)
-bin_count_kernel(const ushort4 *__restrict__ bbox, long long m, uint32_t *__restrict__ ws)
-{
-    __shared__ uint32_t s_col[kMaxBins], s_row[kMaxBins];
-    s_col[threadIdx.x] = 0;
-    s_row[threadIdx.x] = 0;
-    __syncthreads();
-    const long long stride = (long long)gridDim.x * blockDim.x;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
-        const ushort4 b = bbox[i];
-        const int w = (int)b.y - (int)b.x, h = (int)b.w - (int)b.z;
-        if (w <= 0 || h <= 0) continue;
-        for (int c = b.x; c < (int)b.y; ++c) atomicAdd(&s_col[c], 1u);
-        for (int r = b.z; r < (int)b.w; ++r) atomicAdd(&s_row[r], (uint32_t)w);
-    }
-    __syncthreads();
-    if (s_col[threadIdx.x]) atomicAdd(ws + kWsColHist + threadIdx.x, s_col[threadIdx.x]);
-    if (s_row[threadIdx.x]) atomicAdd(ws + kWsRowHist + threadIdx.x, s_row[threadIdx.x]);
-}
+// workspace, in 32-bit words: the two histograms, their exclusive scans (written by the last CTA of
+// bin_count_kernel), the chunk tickets of the two passes, the totals and that kernel's CTA counter
+constexpr int kWsColHist = 0, kWsRowHist = kMaxBins, kWsColExcl = 2 * kMaxBins, kWsRowExcl = 3 * kMaxBins;
+constexpr int kWsTickets = 4 * kMaxBins, kWsColTotal = kWsTickets + 2, kWsCountDone = kWsTickets + 3;
+constexpr int kWsHeader = 4 * kMaxBins + 8;
 
 // exclusive scan of one value per thread over the 256 threads of the CTA; *total = the sum
 __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *s_warp, uint32_t *total)
@@ -83,6 +65,41 @@ __device__ __forceinline__ uint32_t block_exscan(uint32_t v, uint32_t *s_warp, u
     return off + incl - v;
 }
 
+// per-column entry counts and per-row list lengths of the M visible points (any order); the last CTA
+// to finish scans both histograms once for every CTA of the two passes
+__global__ void __launch_bounds__(256)
+bin_count_kernel(const ushort4 *__restrict__ bbox, long long m, uint32_t *__restrict__ ws)
+{
+    __shared__ uint32_t s_col[kMaxBins], s_row[kMaxBins];
+    __shared__ uint32_t s_warp[kBinBlock / 32];
+    __shared__ bool s_last;
+    s_col[threadIdx.x] = 0;
+    s_row[threadIdx.x] = 0;
+    __syncthreads();
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < m; i += stride) {
+        const ushort4 b = bbox[i];
+        const int w = (int)b.y - (int)b.x, h = (int)b.w - (int)b.z;
+        if (w <= 0 || h <= 0) continue;
+        for (int c = b.x; c < (int)b.y; ++c) atomicAdd(&s_col[c], 1u);
+        for (int r = b.z; r < (int)b.w; ++r) atomicAdd(&s_row[r], (uint32_t)w);
+    }
+    __syncthreads();
+    if (s_col[threadIdx.x]) atomicAdd(ws + kWsColHist + threadIdx.x, s_col[threadIdx.x]);
+    if (s_row[threadIdx.x]) atomicAdd(ws + kWsRowHist + threadIdx.x, s_row[threadIdx.x]);
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(ws + kWsCountDone, 1u) == gridDim.x - 1;
+    __syncthreads();
+    if (!s_last) return;
+    __threadfence();
+    uint32_t total;
+    const uint32_t col_excl = block_exscan(gs_ld_volatile_u32(ws + kWsColHist + threadIdx.x), s_warp, &total);
+    ws[kWsColExcl + threadIdx.x] = col_excl;
+    if (threadIdx.x == 0) ws[kWsColTotal] = total;
+    ws[kWsRowExcl + threadIdx.x] = block_exscan(gs_ld_volatile_u32(ws + kWsRowHist + threadIdx.x), s_warp, &total);
+}
+
 // kPass 1: input = depth-ordered points, bins = tile columns, output = 8-byte entries
 // kPass 2: input = those entries,        bins = tile rows,    output = payload + tile starts
 template <int kPass>
@@ -101,29 +118,23 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     __shared__ uint32_t s_colbase[kMaxBins];  // pass 2: first input entry of every column
     __shared__ int s_bound[kMaxBins];         // pass 2: columns that start inside this chunk
     __shared__ int s_nbound;
-    __shared__ uint32_t s_warp[kBinBlock / 32];
     __shared__ unsigned int s_ticket;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    // input entries of this pass; the grid is sized for a capacity, the surplus CTAs leave at once
+    const long long n = (kPass == 1) ? m : (long long)ws[kWsColTotal];
+    if ((long long)blockIdx.x * kBinChunk >= n) return;
     if (tid == 0) {
         s_ticket = atomicAdd(ws + kWsTickets + (kPass - 1), 1u);
         s_nbound = 0;
     }
     for (int i = tid; i < kBinWords * nb; i += kBinBlock) s_mask[i] = 0u;
-
-    // bin bases from the histograms of bin_count_kernel (256 values: cheaper here than a launch)
-    uint32_t col_total, bin_total;
-    const uint32_t col_excl = block_exscan(ws[kWsColHist + tid], s_warp, &col_total);
-    uint32_t bin_excl = col_excl;
-    bin_total = col_total;
-    if (kPass == 2) {
-        s_colbase[tid] = col_excl;
-        bin_excl = block_exscan(ws[kWsRowHist + tid], s_warp, &bin_total);
-    }
-    const long long n = (kPass == 1) ? m : (long long)col_total;  // input entries of this pass
-    const long long chunk = s_ticket;  // written before the barriers inside block_exscan
+    // bin bases: the scans of bin_count_kernel's histograms
+    const uint32_t bin_excl = ws[(kPass == 1 ? kWsColExcl : kWsRowExcl) + tid];
+    if (kPass == 2) s_colbase[tid] = ws[kWsColExcl + tid];
+    __syncthreads();
+    const long long chunk = s_ticket;
     const long long chunk_start = chunk * kBinChunk;
-    if (chunk_start >= n) return;      // launched for a capacity
     const bool last = chunk_start + kBinChunk >= n;
 
     // ---- load: warp w of round j owns the 32 consecutive entries of mask word j * 8 + w ------------
@@ -153,7 +164,6 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
             }
         }
     }
-    __syncthreads();
 
     // ---- mark ------------------------------------------------------------------------------------
     const uint32_t bit = 1u << lane, lt = bit - 1u;

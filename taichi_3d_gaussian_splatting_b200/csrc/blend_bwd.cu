@@ -109,18 +109,28 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const float4 *__restrict__ records, const float *__restrict__ image_grad,
                  const float *__restrict__ acc_alpha, const int32_t *__restrict__ last_effective,
                  float *__restrict__ splat_grads, float *__restrict__ map_on_image,
-                 const uint8_t *__restrict__ cell_masks, const long long mask_stride)
+                 const uint8_t *__restrict__ cell_masks, const long long mask_stride,
+                 GsWorkCounter *__restrict__ work, const unsigned num_units)
 {
-    constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile
+    constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile = units per tile
     constexpr int kPartsPerColumn = kParts / 2;
     __shared__ float4 s_rec_all[kParts][kBatch * 3];
     __shared__ __align__(16) float s_out_all[kParts][kBatch * kGradSlots];
 
-    const int lane = threadIdx.x & 31, part = threadIdx.x >> 5;
-    float4 *s_rec = s_rec_all[part];
-    float *s_out = s_out_all[part];
+    const int lane = threadIdx.x & 31;
+    float4 *s_rec = s_rec_all[threadIdx.x >> 5];
+    float *s_out = s_out_all[threadIdx.x >> 5];
     const int tiles_per_row = width / kTile;
-    const int tile = blockIdx.x;
+    const int my_slot = reduced_slot(lane);
+    // unit = (tile, part).  Persistent launch (work != nullptr): every warp pulls units from the
+    // counter until they run out; otherwise one CTA per tile, warp w takes part w.
+    for (;;) {
+    unsigned unit = blockIdx.x * kParts + (threadIdx.x >> 5);
+    if (work) {
+        unit = gs_next_unit(work);
+        if (unit >= num_units) break;
+    }
+    const int tile = unit / kParts, part = unit % kParts;
     const int tile_u = tile % tiles_per_row, tile_v = tile / tiles_per_row;
     const int col0 = tile_u * kTile + (part / kPartsPerColumn) * kCellW;
     const int row0 = tile_v * kTile + (part % kPartsPerColumn) * (kCells * kCellH);
@@ -146,7 +156,6 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         cell_last[j] = __reduce_max_sync(0xffffffffu, last[j]);
         hi = max(hi, cell_last[j]);
     }
-    const int my_slot = reduced_slot(lane);
 
     // software pipeline: records of the next batch in registers, payload two batches ahead
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
@@ -286,6 +295,10 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             reinterpret_cast<float2 *>(map_on_image)[px] = make_float2(tot0[j], tot1[j]);
         }
     }
+    if (!work) return;
+    __syncwarp();  // the next unit restages s_rec / s_out
+    }
+    gs_retire_warp(work, gridDim.x * kParts);
 }
 
 template <int kCells>
@@ -294,11 +307,33 @@ int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t 
                const float *image_grad, const float *acc_alpha, const int32_t *last_effective,
                float *splat_grads, float *map_on_image, const uint8_t *cell_masks, long long mask_stride)
 {
-    constexpr int kThreads = 32 * (kTilePixels / (kCells * 32));
+    constexpr int kParts = kTilePixels / (kCells * 32);
+    constexpr int kThreads = 32 * kParts;
+    // persistent launch: as many CTAs as are resident at once, warps pull (tile, part) units
+    static int resident[4] = {0, 0, 0, 0};
+    int &res = resident[(map_on_image ? 2 : 0) + (cell_masks ? 1 : 0)];
+    if (res == 0) {
+        int dev = 0, sms = 0, per_sm = 0;
+        GS_CUDA_TRY(cudaGetDevice(&dev));
+        GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+#define GS_BWD_OCC(MAG, MSK) \
+    GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, MAG, MSK>, kThreads, 0))
+        if (map_on_image) {
+            if (cell_masks) GS_BWD_OCC(true, true); else GS_BWD_OCC(true, false);
+        } else {
+            if (cell_masks) GS_BWD_OCC(false, true); else GS_BWD_OCC(false, false);
+        }
+#undef GS_BWD_OCC
+        res = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    const char *pe = getenv("GS_BLEND_PERSISTENT");  // 0: one CTA per tile (A/B and tests; read per call)
+    GsWorkCounter *work = (pe && atoi(pe) == 0) ? nullptr : gs_work_counter(st);
+    const unsigned units = (unsigned)tiles * kParts;
+    const int grid = work ? (tiles < res ? tiles : res) : tiles;
 #define GS_BWD_LAUNCH(MAG, MSK)                                                                        \
-    blend_bwd_kernel<kCells, MAG, MSK><<<tiles, kThreads, 0, st>>>(                                     \
+    blend_bwd_kernel<kCells, MAG, MSK><<<grid, kThreads, 0, st>>>(                                      \
         height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,      \
-        splat_grads, map_on_image, cell_masks, mask_stride)
+        splat_grads, map_on_image, cell_masks, mask_stride, work, units)
     if (map_on_image) {
         if (cell_masks) GS_BWD_LAUNCH(true, true); else GS_BWD_LAUNCH(true, false);
     } else {

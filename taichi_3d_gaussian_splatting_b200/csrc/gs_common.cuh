@@ -3,6 +3,10 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <map>
+#include <mutex>
+#include <utility>
+
 #include "gs_b200.h"
 
 #define GS_LAUNCH_CHECK()                          \
@@ -142,4 +146,70 @@ __device__ __forceinline__ uint32_t gs_ld_volatile_u32(const uint32_t *p)
 __device__ __forceinline__ void gs_st_volatile_u32(uint32_t *p, uint32_t v)
 {
     *reinterpret_cast<volatile uint32_t *>(p) = v;
+}
+
+// ---- work counters of the persistent blend kernels -------------------------------------------------
+// The blend kernels run as many CTAs as fit the machine and every WARP pulls its next unit of work (a
+// quarter / half tile) from a counter, so a warp whose pixels saturate early moves on instead of
+// idling until the slowest warp of its CTA retires.  One {next, done} pair per (device, stream): a
+// stream runs its launches in order and the last warp of a launch resets the pair, so no memset is
+// needed between launches.  nullptr (table full, allocation failed) = the caller launches one CTA per
+// tile instead.
+struct GsWorkCounter {
+    unsigned int next, done;
+};
+
+inline GsWorkCounter *gs_work_counter(cudaStream_t st)
+{
+    constexpr int kSlots = 4096;
+    struct PerDevice {
+        GsWorkCounter *base = nullptr;
+        int used = 0;
+        bool failed = false;
+    };
+    static std::mutex mu;
+    static std::map<int, PerDevice> devices;
+    static std::map<std::pair<int, cudaStream_t>, GsWorkCounter *> table;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) return nullptr;
+    std::lock_guard<std::mutex> lock(mu);
+    auto it = table.find({dev, st});
+    if (it != table.end()) return it->second;
+    PerDevice &d = devices[dev];
+    if (d.failed) return nullptr;
+    if (!d.base) {
+        cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cap) != cudaSuccess || cap != cudaStreamCaptureStatusNone) return nullptr;
+        if (cudaMalloc(&d.base, sizeof(GsWorkCounter) * kSlots) != cudaSuccess ||
+            cudaMemset(d.base, 0, sizeof(GsWorkCounter) * kSlots) != cudaSuccess) {
+            (void)cudaGetLastError();
+            d.failed = true;
+            d.base = nullptr;
+            return nullptr;
+        }
+    }
+    if (d.used >= kSlots) return nullptr;
+    GsWorkCounter *c = d.base + d.used++;
+    table[{dev, st}] = c;
+    return c;
+}
+
+// next unit of the calling warp (all lanes get it); units >= total mean "done"
+__device__ __forceinline__ unsigned gs_next_unit(GsWorkCounter *ctr)
+{
+    unsigned u = 0;
+    if ((threadIdx.x & 31) == 0) u = atomicAdd(&ctr->next, 1u);
+    return __shfl_sync(0xffffffffu, u, 0);
+}
+
+// called once by every warp of the launch when it has run out of units; the last one re-arms the pair
+__device__ __forceinline__ void gs_retire_warp(GsWorkCounter *ctr, unsigned total_warps)
+{
+    if ((threadIdx.x & 31) == 0) {
+        const unsigned d = atomicAdd(&ctr->done, 1u);
+        if (d == total_warps - 1u) {
+            ctr->next = 0u;
+            ctr->done = 0u;
+        }
+    }
 }

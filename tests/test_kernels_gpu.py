@@ -543,9 +543,12 @@ def test_view_sharded_step_on_two_lanes_matches_one_lane():
     g = torch.from_numpy(np.random.default_rng(4).uniform(0, 1, (160, 256, 3)).astype(np.float32)).cuda()
     views = [(0.01 * i, -0.005 * i) for i in range(6)]
     results = []
-    for lanes in (1, 2, 3):
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    for lanes, priority_sections in ((1, False), (2, False), (3, False), (3, True), (1, True)):
         ras = _module()
         t = util.scene_tensors(scene, requires_grad=True)
+        # (3, True): the small kernels of every view on a high-priority companion stream of its lane
+        impl.PRIORITY_SECTIONS = priority_sections
 
         def render(xyz, feat, view, t=t, ras=ras):
             t["t_pointcloud_camera"] = torch.tensor([[view[0], view[1], 0.0]], device="cuda")
@@ -556,6 +559,7 @@ def test_view_sharded_step_on_two_lanes_matches_one_lane():
         res = step(t["point_cloud"], t["point_cloud_features"], views)
         torch.cuda.synchronize()
         assert res.num_local_views == 6
+        impl.PRIORITY_SECTIONS = False
         results.append((t["point_cloud"].grad.clone(), t["point_cloud_features"].grad.clone(), float(res.loss)))
     for gx, gf, loss in results[1:]:
         assert abs(loss - results[0][2]) <= 1e-5 * abs(results[0][2])
@@ -590,6 +594,35 @@ def test_backward_with_and_without_the_forward_cell_masks():
         l2, mx = util.grad_error(b, a)
         assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
     assert np.allclose(grads[0][3], grads[1][3], rtol=1e-4, atol=1e-7)
+
+
+def test_persistent_blend_launch_equals_one_cta_per_tile(monkeypatch):
+    """The backward blend's persistent launch (warps pull (tile, part) units from a per-stream counter
+    that the last warp re-arms) against the plain one-CTA-per-tile launch (GS_BLEND_PERSISTENT=0):
+    gradients equal up to the order of the RED adds, the same pairs visited; repeated launches on one
+    stream and an image with fewer tiles than resident CTAs included."""
+    for (n, w, h, sf) in ((30000, 256, 160, 0.015), (500, 32, 16, 0.05), (200000, 1024, 512, 0.006)):
+        scene = make_scene(n, w, h, seed=41, scale_factor=sf)
+        g = torch.from_numpy(np.random.default_rng(8).uniform(0, 1, (h, w, 3)).astype(np.float32)).cuda()
+        runs = []
+        for mode in ("1", "0", "1"):
+            monkeypatch.setenv("GS_BLEND_PERSISTENT", mode)
+            hooked = {}
+            ras = _module(hook=lambda hk: hooked.update(h=hk))
+            t = util.scene_tensors(scene, requires_grad=True)
+            image, depth, count = _call(ras, scene, t, band=3)
+            (image * g).sum().backward()
+            torch.cuda.synchronize()
+            runs.append((image.detach().cpu().numpy(), depth.detach().cpu().numpy(), count.cpu().numpy(),
+                         t["point_cloud"].grad.cpu().numpy(), t["point_cloud_features"].grad.cpu().numpy(),
+                         hooked["h"].num_affected_pixels.cpu().numpy()))
+        for other in runs[1:]:
+            for a, b in zip(runs[0][:3], other[:3]):
+                assert np.array_equal(a, b)
+            assert np.array_equal(runs[0][5], other[5])
+            for a, b in zip(runs[0][3:5], other[3:5]):
+                l2, mx = util.grad_error(a, b)
+                assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
 
 
 @pytest.mark.parametrize("workload", ["c3_430k_976x544", "c4_2m_976x544", "c5_5m_3840x2160"])
