@@ -109,10 +109,11 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
                 int32_t *__restrict__ payload_out, uint32_t *__restrict__ ws, uint32_t *__restrict__ status,
                 int cols, int rows, uint32_t *__restrict__ starts)
 {
-    extern __shared__ __align__(16) uint32_t smem[];
+    extern __shared__ __align__(16) unsigned long long smem[];
     const int nb = (kPass == 1) ? cols : rows;
-    uint32_t *s_mask = smem;                                               // [kBinWords][nb]
-    uint16_t *s_prefix = reinterpret_cast<uint16_t *>(s_mask + kBinWords * nb);  // [kBinWords][nb]
+    // [kBinWords][nb] pairs: .y = which of the word's 32 entries cover the bin, .x = output position of
+    // the first of them (filled in after the look-back): one 8-byte load per (entry, bin) in the write loop
+    uint2 *s_pair = reinterpret_cast<uint2 *>(smem);
     __shared__ uint32_t s_base[kMaxBins];     // output position of this chunk's first item of a bin
     __shared__ uint32_t s_total[kMaxBins];    // this chunk's items per bin
     __shared__ uint32_t s_colbase[kMaxBins];  // pass 2: first input entry of every column
@@ -128,7 +129,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
         s_ticket = atomicAdd(ws + kWsTickets + (kPass - 1), 1u);
         s_nbound = 0;
     }
-    for (int i = tid; i < kBinWords * nb; i += kBinBlock) s_mask[i] = 0u;
+    for (int i = tid; i < kBinWords * nb; i += kBinBlock) smem[i] = 0ull;
     // bin bases: the scans of bin_count_kernel's histograms
     const uint32_t bin_excl = ws[(kPass == 1 ? kWsColExcl : kWsRowExcl) + tid];
     if (kPass == 2) s_colbase[tid] = ws[kWsColExcl + tid];
@@ -169,8 +170,8 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     const uint32_t bit = 1u << lane, lt = bit - 1u;
 #pragma unroll
     for (int j = 0; j < kBinItems; ++j) {
-        uint32_t *w = s_mask + (j * (kBinBlock / 32) + warp) * nb;
-        for (int b = lo[j]; b <= hi[j]; ++b) atomicOr(w + b, bit);
+        uint2 *w = s_pair + (j * (kBinBlock / 32) + warp) * nb;
+        for (int b = lo[j]; b <= hi[j]; ++b) atomicOr(&w[b].y, bit);
     }
     __syncthreads();
 
@@ -178,10 +179,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     if (tid < nb) {
         uint32_t run = 0;
 #pragma unroll 8
-        for (int w = 0; w < kBinWords; ++w) {
-            s_prefix[w * nb + tid] = (uint16_t)run;
-            run += (uint32_t)__popc(s_mask[w * nb + tid]);
-        }
+        for (int w = 0; w < kBinWords; ++w) run += (uint32_t)__popc(s_pair[w * nb + tid].y);
         s_total[tid] = run;
         uint32_t *my = status + chunk * nb + tid;
         gs_st_volatile_u32(my, (chunk == 0 ? kBinPrefix : kBinAggregate) | run);
@@ -207,7 +205,13 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
             }
             gs_st_volatile_u32(my, kBinPrefix | (excl + run));
         }
-        s_base[tid] = bin_excl + excl;
+        uint32_t off = bin_excl + excl;
+        s_base[tid] = off;
+#pragma unroll 8
+        for (int w = 0; w < kBinWords; ++w) {
+            s_pair[w * nb + tid].x = off;
+            off += (uint32_t)__popc(s_pair[w * nb + tid].y);
+        }
     }
     if (kPass == 2 && tid < cols) {
         const long long v = (long long)s_colbase[tid];
@@ -220,8 +224,8 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     for (int j = 0; j < kBinItems; ++j) {
         const int word = j * (kBinBlock / 32) + warp;
         for (int b = lo[j]; b <= hi[j]; ++b) {
-            const int idx = word * nb + b;
-            const uint32_t pos = s_base[b] + (uint32_t)s_prefix[idx] + (uint32_t)__popc(s_mask[idx] & lt);
+            const uint2 pm = s_pair[word * nb + b];
+            const uint32_t pos = pm.x + (uint32_t)__popc(pm.y & lt);
             if (kPass == 1) entries_out[pos] = value[j];
             else payload_out[pos] = (int32_t)(uint32_t)value[j];
         }
@@ -234,14 +238,14 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
             const int c = s_bound[q];
             const uint32_t eb = (uint32_t)((long long)s_colbase[c] - chunk_start);
             if (tid < rows) {
-                uint32_t before;
+                uint32_t at;
                 if (eb >= (uint32_t)kBinChunk) {
-                    before = s_total[tid];
+                    at = s_base[tid] + s_total[tid];
                 } else {
-                    const int idx = (int)(eb >> 5) * nb + tid;
-                    before = (uint32_t)s_prefix[idx] + (uint32_t)__popc(s_mask[idx] & ((1u << (eb & 31u)) - 1u));
+                    const uint2 pm = s_pair[(int)(eb >> 5) * nb + tid];
+                    at = pm.x + (uint32_t)__popc(pm.y & ((1u << (eb & 31u)) - 1u));
                 }
-                starts[(size_t)tid * cols + c] = s_base[tid] + before;
+                starts[(size_t)tid * cols + c] = at;
             }
         }
     }
@@ -269,7 +273,7 @@ inline int64_t bin_entry_capacity(int64_t m, int64_t k, int cols)
     return k < by_cols ? k : by_cols;           // ... and at least one row per entry
 }
 
-inline size_t bin_smem(int nb) { return (size_t)kBinWords * nb * 6; }
+inline size_t bin_smem(int nb) { return (size_t)kBinWords * nb * 8; }
 
 }  // namespace
 
