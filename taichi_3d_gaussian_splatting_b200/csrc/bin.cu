@@ -100,6 +100,10 @@ bin_count_kernel(const ushort4 *__restrict__ bbox, long long m, uint32_t *__rest
     ws[kWsRowExcl + threadIdx.x] = block_exscan(gs_ld_volatile_u32(ws + kWsRowHist + threadIdx.x), s_warp, &total);
 }
 
+constexpr int kBinStageBytes = 32768;  // shared-memory staging of a chunk's output
+template <int kPass> struct BinOut { typedef unsigned long long type; };
+template <> struct BinOut<2> { typedef int32_t type; };
+
 // kPass 1: input = depth-ordered points, bins = tile columns, output = 8-byte entries
 // kPass 2: input = those entries,        bins = tile rows,    output = payload + tile starts
 template <int kPass>
@@ -120,6 +124,9 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     __shared__ int s_bound[kMaxBins];         // pass 2: columns that start inside this chunk
     __shared__ int s_nbound;
     __shared__ unsigned int s_ticket;
+    __shared__ uint32_t s_loc[kMaxBins];      // chunk-local position of a bin's first item
+    __shared__ uint32_t s_adj[kMaxBins];
+    __shared__ uint32_t s_warp[kBinBlock / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     // input entries of this pass; the grid is sized for a capacity, the surplus CTAs leave at once
@@ -220,15 +227,53 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     __syncthreads();
 
     // ---- write -----------------------------------------------------------------------------------
-#pragma unroll
-    for (int j = 0; j < kBinItems; ++j) {
-        const int word = j * (kBinBlock / 32) + warp;
-        for (int b = lo[j]; b <= hi[j]; ++b) {
-            const uint2 pm = s_pair[word * nb + b];
-            const uint32_t pos = pm.x + (uint32_t)__popc(pm.y & lt);
-            if (kPass == 1) entries_out[pos] = value[j];
-            else payload_out[pos] = (int32_t)(uint32_t)value[j];
+    // A direct store per (entry, bin) would scatter 4 / 8 bytes to a different list per lane (one 32-byte
+    // sector each: 2.5 of 3.6 ms at 5M points / 3840x2160).  The chunk's output is laid out bin by bin in
+    // shared memory instead and every bin's run (~50 items) is copied out as one contiguous piece; when
+    // the chunk's output exceeds the staging buffer the bins are taken in groups that fit.
+    typedef typename BinOut<kPass>::type OutT;
+    OutT *s_stage = reinterpret_cast<OutT *>(smem + kBinWords * nb);
+    constexpr uint32_t kCap = kBinStageBytes / sizeof(OutT);
+    uint32_t num_out;
+    {
+        const uint32_t loc = block_exscan(tid < nb ? s_total[tid] : 0u, s_warp, &num_out);
+        if (tid < nb) {
+            s_loc[tid] = loc;
+            s_adj[tid] = loc - s_base[tid];  // chunk-local position = global position + s_adj (mod 2^32)
         }
+    }
+    __syncthreads();
+    OutT *out = (kPass == 1) ? reinterpret_cast<OutT *>(entries_out) : reinterpret_cast<OutT *>(payload_out);
+    for (int gs = 0; gs < nb;) {
+        const uint32_t first = s_loc[gs];
+        int ge = nb;
+        if (num_out - first > kCap) {  // the largest ge whose bins [gs, ge) fit (a bin holds <= kBinChunk items)
+            int lo_g = gs + 1, hi_g = nb - 1;
+            while (lo_g < hi_g) {
+                const int mid = (lo_g + hi_g + 1) >> 1;
+                if (s_loc[mid] - first <= kCap) lo_g = mid; else hi_g = mid - 1;
+            }
+            ge = lo_g;
+        }
+#pragma unroll
+        for (int j = 0; j < kBinItems; ++j) {
+            const int word = j * (kBinBlock / 32) + warp;
+            const int b1 = min(hi[j], ge - 1);
+            for (int b = max(lo[j], gs); b <= b1; ++b) {
+                const uint2 pm = s_pair[word * nb + b];
+                const uint32_t pos = pm.x + (uint32_t)__popc(pm.y & lt);
+                s_stage[pos + s_adj[b] - first] = (OutT)value[j];
+            }
+        }
+        __syncthreads();
+        for (int bb = gs + warp; bb < ge; bb += kBinBlock / 32) {
+            const OutT *src = s_stage + (s_loc[bb] - first);
+            OutT *dst = out + s_base[bb];
+            const uint32_t cnt = s_total[bb];
+            for (uint32_t i = lane; i < cnt; i += 32) dst[i] = src[i];
+        }
+        gs = ge;
+        if (gs < nb) __syncthreads();
     }
 
     // ---- pass 2: where every (row, column) tile starts, for the columns that begin in this chunk ----
@@ -273,7 +318,7 @@ inline int64_t bin_entry_capacity(int64_t m, int64_t k, int cols)
     return k < by_cols ? k : by_cols;           // ... and at least one row per entry
 }
 
-inline size_t bin_smem(int nb) { return (size_t)kBinWords * nb * 8; }
+inline size_t bin_smem(int nb) { return (size_t)kBinWords * nb * 8 + kBinStageBytes; }
 
 }  // namespace
 
