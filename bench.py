@@ -12,7 +12,8 @@ prescribes.  Views cycle through a small set of nearby camera poses.
   e2e     the same through the public module with HOST inputs: per step the camera pose and the
           per-pixel loss weights come from pinned host memory (what the reference's trainer
           uploads per step, Tr.py:149-159: pose + ground-truth image; the Gaussians are
-          nn.Parameters resident on the GPU, Tr.py:65-98) and the scalar loss is read back
+          nn.Parameters resident on the GPU, Tr.py:65-98) and the scalar loss is read back every
+          step (asynchronous copy into pinned memory, consumed one step later, as a trainer logs it)
   N > 1   views are sharded over ranks against a replicated cloud; every step ends with an NCCL
           all-reduce of the N x 59 gradient; weak scaling
   --impl reference   the CPU oracle (the reference's Taichi kernels cannot run here: no Taichi)
@@ -361,6 +362,8 @@ def run_b200(args):
     num_slots = 2 * lanes                                      # e2e: staging buffers of the targets
     wt_stage = [torch.empty_like(wt_dev) for _ in range(num_slots)]
     uploads, finished, next_upload = {}, {}, [0]
+    loss_host = [torch.zeros(1, dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ready, loss_log = [None, None], []
 
     def upload(g):
         """pose + target of the g-th view this rank renders, from pinned host memory, on the copy
@@ -402,7 +405,18 @@ def run_b200(args):
 
         total = run_views(per_view)
         finish_step()
-        return float(total.item())  # device -> host read of the step's result
+        # device -> host read of the step's result, every step, the way a trainer logs a loss: an
+        # asynchronous copy into pinned memory, consumed one step later (the host never stalls the
+        # queue; the last read completes before the timed region's closing synchronize)
+        slot = i % 2
+        loss_host[slot].copy_(total.detach().reshape(1), non_blocking=True)
+        loss_ready[slot] = torch.cuda.Event()
+        loss_ready[slot].record(torch.cuda.current_stream(dev))
+        prev = loss_ready[1 - slot]
+        if prev is not None:
+            prev.synchronize()
+            loss_log.append(float(loss_host[1 - slot][0]))
+        return None
 
     def step_render(i):
         v = view_of(i, 0)
@@ -561,7 +575,9 @@ def run_b200(args):
                    "l2": "inputs exceed L2 (236 MB of point data read per step)"},
         "e2e": {"value": iters / (ms_e2e * 1e-3), "unit": "it/s",
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": 4,
-                "ms_per_step": ms_e2e / args.steps},
+                "ms_per_step": ms_e2e / args.steps,
+                "loss_readback": "every step, asynchronous copy into pinned memory, read one step later",
+                "losses_read": len(loss_log)},
         "render_mpix_per_s": world * args.steps * hw / (ms_render * 1e-3) / 1e6,
         "render_ms_per_frame": ms_render / args.steps,
         "gpu_launches": launches_per_step * VIEWS_PER_RANK * args.steps,
