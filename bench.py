@@ -290,7 +290,7 @@ def run_b200(args):
     # over ranks against a replicated cloud): forward+backward of every view, the point gradients
     # summed into one N x 59 buffer by the backward itself, then ONE all-reduce of that buffer.
     flat = torch.zeros(n * 59, dtype=torch.float32, device=dev)
-    gx, gf = flat[:3 * n].view(n, 3), flat[3 * n:].view(n, 56)
+    gf, gx = flat[:56 * n].view(n, 56), flat[56 * n:].view(n, 3)   # 16-byte aligned feature rows for every n
     ras.accumulate_gradients_into(gx, gf)
     copy_stream = torch.cuda.Stream(dev)
 

@@ -607,7 +607,22 @@ void FN(blend_bwd)(int height, int width, const int32_t *tile_start, const int32
                 real dpc[4] = {hp * t2[0], hp * t2[1], hp * t2[2], hp * t2[3]};
                 real aa = alpha_act[gidx];
                 real prod = p * aa;
-                if (prod >= (real)1. / (real)255.) {
+#ifdef GSO_DOUBLE
+                /* The fp64 build is the arbiter of gradient VALUES; which pairs take part is the
+                 * reference's fp32 decision (R.py:634 on fp32 values), so it is taken here with the
+                 * same float arithmetic as the fp32 build (the inputs are fp32 values widened). */
+                float fdx = (pu + 0.5f) - (float)point_uv[2 * gidx];
+                float fdy = (pv + 0.5f) - (float)point_uv[2 * gidx + 1];
+                float fc0 = (float)c[0], fc1 = (float)c[1], fc2 = (float)c[2];
+                float fv0 = fc0 * fdx + fc1 * fdy;
+                float fv1 = fc1 * fdx + fc2 * fdy;
+                float fquad = fdx * fv0 + fdy * fv1;
+                float fprod = (gso_expf(-0.5f * fquad) * (float)c[3]) * (float)aa;
+                int take = fprod >= 1.f / 255.f;
+#else
+                int take = prod >= (real)1. / (real)255.;
+#endif
+                if (take) {
                     real a = R_FMIN(prod, (real)0.99);
                     const real *col = color + 3 * gidx;
                     T = T / ((real)1. - a);

@@ -51,6 +51,10 @@ KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "binned")
 # between forward and backward); 0 makes it recompute them
 REUSE_CELL_MASKS = os.environ.get("GS_REUSE_CELL_MASKS", "1") != "0"
 
+# operator calls made through this module since import (acceptance tests check that the reference's
+# unchanged callers really ran THIS code)
+CALL_COUNTS = {"forward": 0, "backward": 0, "hook": 0}
+
 # set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
 STAGE_PROFILER = None
 
@@ -235,6 +239,9 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                 ctx.set_materialize_grads(False)
                 ctx.camera_info = camera_info
                 ctx.color_max_sh_band = color_max_sh_band
+                # where this call's gradients go is fixed NOW: a later accumulate_gradients_into()
+                # (or another user of the module) must not redirect a backward already recorded
+                ctx.accumulate_into = outer._accumulate_into
                 # the outputs must not be reachable from ctx (output -> grad_fn -> ctx cycle)
                 image, depth, count = out.image, out.depth, out.count
                 out.image = out.depth = out.count = None
@@ -255,7 +262,7 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                         t_pointcloud_camera, ctx.camera_info, ctx.color_max_sh_band,
                         grad_rasterized_image, backward_valid_point_hook,
                         GaussianPointCloudRasterisation.BackwardValidPointHookInput,
-                        accumulate_into=outer._accumulate_into)
+                        accumulate_into=ctx.accumulate_into)
                 return grad_pointcloud, grad_pointcloud_features, None, None, None, None, None, None
 
         self._module_function = _module_function
@@ -268,6 +275,9 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
         ([N,3] and [N,56], contiguous, zeroed by the caller once per batch) and returns no gradient
         to autograd for those two inputs -- so a batch of views costs neither a zero fill nor an
         AccumulateGrad pass per view.  Call with (None, None) to restore the reference behaviour.
+        The target is captured by each forward call: a backward always adds into the buffers that
+        were set when ITS forward ran.  The rows are written as 16-byte vectors, so both buffers
+        must start on a 16-byte boundary (a flat N x 59 buffer must hold the N x 56 block first).
         """
         if grad_point_cloud is None or grad_point_cloud_features is None:
             self._accumulate_into = None
@@ -276,6 +286,9 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
             if not (t.is_cuda and t.dtype == torch.float32 and t.dim() == 2 and t.shape[1] == cols
                     and t.is_contiguous()):
                 raise ValueError("gradient buffers must be contiguous CUDA float32 [N,3] and [N,56]")
+        if grad_point_cloud_features.data_ptr() % 16:
+            raise ValueError("grad_point_cloud_features must be 16-byte aligned (rows are added with "
+                             "red.global.add.v4.f32); put the N x 56 block first in a flat buffer")
         self._accumulate_into = (grad_point_cloud, grad_point_cloud_features)
 
     def forward(self, input_data: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput"):
@@ -362,6 +375,7 @@ def _check_inputs(pointcloud, features, invalid_mask, object_id, q, t, intrinsic
 def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
                   q_pointcloud_camera, t_pointcloud_camera, camera_info,
                   keep_unsorted: bool = False, keep_cell_masks: bool = False) -> _ForwardState:
+    CALL_COUNTS["forward"] += 1
     dev = pointcloud.device
     intrinsics = camera_info.camera_intrinsics
     _check_inputs(pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
@@ -541,6 +555,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
 def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, point_object_id,
                    t_pointcloud_camera, camera_info, color_max_sh_band, grad_rasterized_image,
                    hook, hook_input_type, accumulate_into=None):
+    CALL_COUNTS["backward"] += 1
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
     s_big = torch.cuda.current_stream(dev)
@@ -592,6 +607,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
         _hand_over(s_small, s_big)
     _mark("point_bwd")
     if want_hook:
+        CALL_COUNTS["hook"] += 1
         point_in_camera = buf.view("point_in_camera", m)
         hook(hook_input_type(
             point_id_in_camera_list=buf.view("ids", m),
@@ -611,15 +627,40 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
 
 
 def install() -> None:
-    """Make the reference package use this operator (trainer, renderer and tests unchanged).
+    """Make the reference package use this operator: GaussianPointTrainer, gaussian_point_render.py,
+    visualizer / benchmark scripts and the reference's tests then run unchanged.
 
-    Replaces the class attribute in the already-importable reference module; raises ImportError
-    if the reference package (and its Taichi dependency) is not importable.
-    """
+        import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as drop_in
+        drop_in.install()          # any time: before or after the callers are imported
+
+    What it does, in the already importable reference package (raises ImportError otherwise):
+      * `taichi_3d_gaussian_splatting.GaussianPointCloudRasterisation.GaussianPointCloudRasterisation`
+        and `.find_tile_start_and_end` become this module's;
+      * every loaded module that already did `from ... import GaussianPointCloudRasterisation` (the
+        trainer, the renderer, a test module) is re-pointed too, so the call order does not matter;
+      * this class ADOPTS the reference's own nested record types (`...Config`, `...Input`,
+        `BackwardValidPointHookInput`): a `TrainConfig` built earlier (its `default_factory`,
+        GaussianPointTrainer.py:56-57), a YAML round trip through the reference's YAMLWizard base and
+        `isinstance` checks in the callers all keep working on the very same classes.
+    Idempotent."""
     import importlib
+    import sys
     ref = importlib.import_module("taichi_3d_gaussian_splatting.GaussianPointCloudRasterisation")
+    old_cls = ref.GaussianPointCloudRasterisation
+    old_find = getattr(ref, "find_tile_start_and_end", None)
+    if old_cls is GaussianPointCloudRasterisation:
+        return
+    for name in ("GaussianPointCloudRasterisationConfig", "GaussianPointCloudRasterisationInput",
+                 "BackwardValidPointHookInput"):
+        setattr(GaussianPointCloudRasterisation, name, getattr(old_cls, name))
     ref.GaussianPointCloudRasterisation = GaussianPointCloudRasterisation
     ref.find_tile_start_and_end = find_tile_start_and_end
-    pkg = importlib.import_module("taichi_3d_gaussian_splatting")
-    if hasattr(pkg, "GaussianPointCloudRasterisation"):
-        setattr(pkg, "GaussianPointCloudRasterisation", ref)
+    for mod in list(sys.modules.values()):
+        names = getattr(mod, "__dict__", None)
+        if not isinstance(names, dict) or mod is sys.modules[__name__]:
+            continue
+        for attr, val in list(names.items()):
+            if val is old_cls:
+                names[attr] = GaussianPointCloudRasterisation
+            elif old_find is not None and val is old_find:
+                names[attr] = find_tile_start_and_end

@@ -370,13 +370,14 @@ extern "C" int gs_bin_tiles(const int32_t *order, const uint16_t *bbox, int64_t 
     uint32_t *starts = status2 + chunks2 * rows;   // fully written by pass 2: not cleared
     GS_CUDA_TRY(cudaMemsetAsync(ws, 0, (size_t)(kWsHeader + chunks1 * cols + chunks2 * rows) * 4, st));
 
-    static bool attr_set = false;
-    if (!attr_set) {
+    static GsPerDeviceOnce attr_set;
+    int dev = 0;
+    if (attr_set.need(dev)) {
         GS_CUDA_TRY(cudaFuncSetAttribute(bin_pass_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)bin_smem(kMaxBins, true)));
         GS_CUDA_TRY(cudaFuncSetAttribute(bin_pass_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)bin_smem(kMaxBins, true)));
-        attr_set = true;
+        attr_set.mark(dev);
     }
     const ushort4 *boxes = reinterpret_cast<const ushort4 *>(bbox);
     int count_blocks = (int)((m + 255) / 256);

@@ -2,6 +2,11 @@
 //
 // Fast-fp32 profile (FMA contraction, ex2.approx, rcp.approx): gradients are compared with the
 // oracle at 1e-4 relative, the atomic summation order differs from the reference anyway.
+// The DECISION whether a (pixel, entry) pair takes part (alpha >= 1/255, R.py:634) is nevertheless
+// the reference's: a pair whose fast alpha lies within a per-entry error band of 1/255, and every
+// pair of an entry with an irregular conic / non-finite field, is re-decided with the reference's
+// backward arithmetic in literal fp32 (literal_alpha below = utils.py:331-345 with gs_expf), so
+// the set of contributing pairs -- num_affected_pixels -- equals the literal-fp32 oracle's exactly.
 //
 // Instruction-issue bound like the forward blend, and laid out the same way: one WARP owns a
 // column of kCells cells of 8x4 pixels (kCells = 4: an 8x16 half tile); lane l owns pixel
@@ -53,6 +58,30 @@ __device__ __forceinline__ float fast_sqrt(float x)
     float y;
     asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
     return y;
+}
+
+// alpha of a pair exactly as the reference's backward forms it (utils.py:331-345, R.py:628-631) in
+// literal fp32: v = conic d (Taichi's mat @ vec: a[i,0] b[0] + a[i,1] b[1]), quad = d . v,
+// p = exp(-0.5 quad) rescale, alpha = p opacity.  _rn intrinsics are never contracted.
+__device__ __forceinline__ float literal_alpha(float dx, float dy, float a, float b, float c,
+                                               float rescale, float opacity)
+{
+    const float v0 = __fadd_rn(__fmul_rn(a, dx), __fmul_rn(b, dy));
+    const float v1 = __fadd_rn(__fmul_rn(b, dx), __fmul_rn(c, dy));
+    const float quad = __fadd_rn(__fmul_rn(dx, v0), __fmul_rn(dy, v1));
+    return __fmul_rn(__fmul_rn(gs_expf(__fmul_rn(-0.5f, quad)), rescale), opacity);
+}
+
+// Relative half-width of the band around 1/255 inside which the fast alpha (FMA-contracted quadratic
+// form, ex2.approx, pre-multiplied peak) and the literal one may fall on different sides.  The two
+// exponents differ by at most ~5e-7 of the sum P of the magnitudes of the quadratic form's terms, and
+// P <= quad (1 + rho) / (1 - rho) <= 4 quad a c / (a c - b^2) with rho = |b| / sqrt(a c); near the
+// threshold quad = 2 ln(255 peak) <= 11.1.  The constants leave a factor > 4 of slack; the exp
+// approximations and the products add < 2e-6.
+__device__ __forceinline__ float decision_band(float a, float b, float c)
+{
+    const float ac = a * c;
+    return fmaf(2.7e-5f, ac * fast_rcp(ac - b * b), 3e-6f);
 }
 
 // Sum 10 per-lane values over the 32 lanes of a warp with 12 shuffles.  On return v[0] of lane L
@@ -174,31 +203,36 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         // ---- stage: lane l holds entry top-1-l (reverse order) ---------------------------------
         const int my_i = top - 1 - lane;
         const int my_g = g_cur;
-        unsigned my_mask = 0u;
+        unsigned my_mask = 0u;  // cell bits | kCellMaskIrregular
         if (my_i >= start) {
             unsigned live = 0u;
 #pragma unroll
             for (int j = 0; j < kCells; ++j) live |= (my_i < cell_last[j] ? 1u : 0u) << j;
             if (live) {
+                unsigned m = 0u;
                 if (kMasks) {
                     // the forward's culling bits for these cells: plane q = 2 * column + row half
-                    // of the tile's 8x8 quarters, two bits (upper / lower 8x4 cell) per entry
-                    unsigned m = 0u;
+                    // of the tile's 8x8 quarters, two bits (upper / lower 8x4 cell) per entry, and
+                    // the entry's irregular flag
+                    unsigned irr = 0u;
 #pragma unroll
                     for (int h = 0; h < kCells / 2; ++h) {
                         const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * (kCells / 2) + h;
-                        m |= ((unsigned)__ldg(cell_masks + q * mask_stride + my_i) & 3u) << (2 * h);
+                        const unsigned byte = (unsigned)__ldg(cell_masks + q * mask_stride + my_i);
+                        m |= (byte & 3u) << (2 * h);
+                        irr |= byte & kMaskByteIrregular;
                     }
-                    my_mask = live & m;
+                    if (irr) m |= kCellMaskIrregular;
                 } else {
-                    my_mask = live & gs_cell_mask<kCells>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z,
-                                                          x_first, y_first);  // (drops the irregular flag)
+                    m = gs_entry_mask<kCells>(n0, n1, n2, x_first, y_first);
                 }
+                if (live & m) my_mask = (live & m) | (m & kCellMaskIrregular);
             }
         }
         s_rec[3 * lane] = n0;
         s_rec[3 * lane + 1] = n1;
-        s_rec[3 * lane + 2] = n2;
+        // the record's pad word carries the entry's decision band to the visits
+        s_rec[3 * lane + 2] = make_float4(n2.x, n2.y, n2.z, decision_band(n0.z, n0.w, n1.x));
         s_out[kGradSlots * lane + 10] = 0.f;
         // ---- prefetch the next batch -----------------------------------------------------------
         {
@@ -220,10 +254,15 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             const int i = top - 1 - k;
             const float4 r0 = s_rec[3 * k];      // u v a b
             const float4 r1 = s_rec[3 * k + 1];  // c rescale alpha red
-            const float4 r2 = s_rec[3 * k + 2];  // green blue z pad
+            const float4 r2 = s_rec[3 * k + 2];  // green blue z band
             const float dx = fx - r0.x;
             const float adx = r0.z * dx, bdx = r0.w * dx;
             const float peak = r1.y * r1.z;
+            // fast alpha decides outside [lo, hi); inside, and for irregular entries (hi = NaN: no
+            // alpha is ever "safely above"), the literal arithmetic does
+            const bool irregular = (m & kCellMaskIrregular) != 0u;  // warp-uniform
+            const float lo = irregular ? -__int_as_float(0x7f800000) : fmaf(-r2.w, 1.0f / 255.0f, 1.0f / 255.0f);
+            const float hi = irregular ? __int_as_float(0x7fc00000) : fmaf(r2.w, 1.0f / 255.0f, 1.0f / 255.0f);
             float v[10];
 #pragma unroll
             for (int q = 0; q < 10; ++q) v[q] = 0.f;
@@ -235,8 +274,14 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                 const float v0 = fmaf(r0.w, dy, adx);
                 const float v1 = fmaf(r1.x, dy, bdx);
                 const float quad = fmaf(dy, v1, dx * v0);
-                const float prod = fast_ex2(-0.72134752044448170368f * quad) * peak;  // alpha
-                if ((i < last[j]) && (prod >= 1.0f / 255.0f)) {
+                float prod = fast_ex2(-0.72134752044448170368f * quad) * peak;  // alpha
+                bool take = prod >= lo;
+                if (!(prod >= hi) && (take || irregular)) {  // rare: on the edge, or an irregular entry
+                    const float lit = literal_alpha(dx, dy, r0.z, r0.w, r1.x, r1.y, r1.z);
+                    take = lit >= 1.0f / 255.0f;
+                    if (irregular) prod = lit;  // +inf / NaN handling of the literal exp
+                }
+                if ((i < last[j]) && take) {
                     hits += 1;
                     const float a = fminf(prod, 0.99f);
                     const float inv = fast_rcp(1.0f - a);

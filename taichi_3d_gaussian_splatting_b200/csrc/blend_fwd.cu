@@ -240,11 +240,7 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         unsigned my_mask = 0u;
         if (base + lane < end) {
             // culling bits per 8x4 cell (two per pair cell); a pair cell is visited if either is set
-            unsigned fine =
-                gs_cell_mask<2 * kPairs, kCellH>(n0.x, n0.y, n0.z, n0.w, n1.x, n1.y * n1.z, x_first, y_first);
-            // non-finite colour / depth / opacity: the packed path's "add zero" is not a no-op
-            if (!isfinite(((n1.y + n1.z) + (n1.w + n2.x)) + (n2.y + n2.z)))
-                fine = ((1u << (2 * kPairs)) - 1u) | kCellMaskIrregular;
+            const unsigned fine = gs_entry_mask<2 * kPairs>(n0, n1, n2, x_first, y_first);
             unsigned raw = fine & kCellMaskIrregular;
 #pragma unroll
             for (int c = 0; c < kPairs; ++c) raw |= ((fine >> (2 * c)) & 3u) ? (1u << c) : 0u;
@@ -254,7 +250,8 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
 #pragma unroll
                 for (int c = 0; c < kPairs; ++c) {
                     const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * kPairs + c;
-                    cell_masks[q * mask_stride + base + lane] = (uint8_t)((fine >> (2 * c)) & 3u);
+                    cell_masks[q * mask_stride + base + lane] =
+                        (uint8_t)(((fine >> (2 * c)) & 3u) | ((fine & kCellMaskIrregular) ? kMaskByteIrregular : 0u));
                 }
             }
             my_mask = (raw & open) ? (raw & (open | kCellMaskIrregular)) : 0u;

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <map>
 #include <mutex>
 #include <utility>
@@ -21,6 +22,21 @@
         if (e__ != cudaSuccess) return (int)e__;   \
     } while (0)
 
+// Function attributes (opt-in dynamic shared memory) and occupancy numbers are PER DEVICE: a process
+// that drives several GPUs must set / query them once on each.  Bit d of `done` = done on device d.
+struct GsPerDeviceOnce {
+    std::atomic<unsigned long long> done{0ull};
+    bool need(int &dev)
+    {
+        if (cudaGetDevice(&dev) != cudaSuccess) dev = 0;
+        return dev < 0 || dev >= 64 || !((done.load(std::memory_order_acquire) >> dev) & 1ull);
+    }
+    void mark(int dev)
+    {
+        if (dev >= 0 && dev < 64) done.fetch_or(1ull << dev, std::memory_order_release);
+    }
+};
+
 constexpr int kTile = GS_TILE;
 constexpr int kTilePixels = GS_TILE * GS_TILE;
 constexpr int kRecFloats = GS_RECORD_FLOATS;
@@ -28,13 +44,14 @@ constexpr int kGradSlots = GS_GRAD_SLOTS;
 
 // exp of the literal-fp32 profile: Cody-Waite reduction + Cephes polynomial with fma at
 // fixed places.  Must stay operation-for-operation identical to gso_expf in
-// oracle/gs_oracle.c (the translation units that use it are built with -fmad=false, so
-// only the explicit fmaf calls fuse).
+// oracle/gs_oracle.c.  Written with the _rn intrinsics, which the compiler never contracts, so the
+// result has the same bits in a unit built with -fmad=false (project.cu, blend_fwd.cu) and in a
+// fast-fp32 unit (blend_bwd.cu, which re-decides pairs on the alpha = 1/255 edge with it).
 __device__ __forceinline__ float gs_expf_core(float x)
 {
-    float t = x * 1.44269504088896341f;
-    float tj = t + 12582912.0f;  // 1.5 * 2^23: the low mantissa bits of tj hold rint(t)
-    float j = tj - 12582912.0f;
+    float t = __fmul_rn(x, 1.44269504088896341f);
+    float tj = __fadd_rn(t, 12582912.0f);  // 1.5 * 2^23: the low mantissa bits of tj hold rint(t)
+    float j = __fsub_rn(tj, 12582912.0f);
     float f = fmaf(j, -0.693145751953125f, x);
     f = fmaf(j, -1.42860682030941723212e-6f, f);
     float p = 1.9875691500e-4f;
@@ -43,8 +60,8 @@ __device__ __forceinline__ float gs_expf_core(float x)
     p = fmaf(p, f, 4.1665795894e-2f);
     p = fmaf(p, f, 1.6666665459e-1f);
     p = fmaf(p, f, 5.0000001201e-1f);
-    float f2 = f * f;
-    float r = fmaf(p, f2, f) + 1.0f;
+    float f2 = __fmul_rn(f, f);
+    float r = __fadd_rn(fmaf(p, f2, f), 1.0f);
     // (int)j << 23 without the conversion: bits(tj) = 0x4B400000 + j and 0x4B400000 << 23 == 0 (mod 2^32)
     return __int_as_float(__float_as_int(r) + (__float_as_int(tj) << 23));
 }
@@ -130,6 +147,24 @@ __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, floa
     }
     return mask;
 }
+
+// The culling bits of one staged list entry (48-byte record r0 = u v a b, r1 = c rescale opacity red,
+// r2 = green blue depth pad) for a warp's kCells cells, as BOTH blend kernels must see them: entries
+// with a conic that is not positive definite / finite, or with a non-finite colour / depth / opacity,
+// keep every bit and carry kCellMaskIrregular -- they take the guarded literal arithmetic in the forward
+// (the masked "add zero" of the packed path is not a no-op for them) and in the backward (the decision
+// alpha >= 1/255 is then taken with the literal exp, never with ex2.approx of a positive / NaN exponent).
+template <int kCells>
+__device__ __forceinline__ unsigned gs_entry_mask(const float4 &r0, const float4 &r1, const float4 &r2,
+                                                  float x_first, float y_first)
+{
+    unsigned fine = gs_cell_mask<kCells, kCellH>(r0.x, r0.y, r0.z, r0.w, r1.x, r1.y * r1.z, x_first, y_first);
+    if (!isfinite(((r1.y + r1.z) + (r1.w + r2.x)) + (r2.y + r2.z)))
+        fine = ((1u << kCells) - 1u) | kCellMaskIrregular;
+    return fine;
+}
+// bit of a cell_masks byte (two culling bits per 8x8 quarter in bits 0-1) that carries kCellMaskIrregular
+constexpr unsigned kMaskByteIrregular = 4u;
 
 __device__ __forceinline__ unsigned long long gs_ld_volatile_u64(const unsigned long long *p)
 {

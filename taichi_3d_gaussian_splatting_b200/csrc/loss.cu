@@ -518,12 +518,13 @@ extern "C" int gs_loss_fwd(const float *image, int64_t image_stride_h, int64_t i
     if (height < kWin || width < kWin) return GS_E_INVALID;
     if (features && (!invalid_mask || n < 0)) return GS_E_INVALID;
     cudaStream_t st = (cudaStream_t)stream;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static GsPerDeviceOnce attr_set;
+    int dev = 0;
+    if (attr_set.need(dev)) {
         const cudaError_t e =
             cudaFuncSetAttribute(loss_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kFwdSmem);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_set.mark(dev);
     }
     const dim3 grid(tiles_of(width - (kWin - 1)), tiles_of(height - (kWin - 1)));
     const int blocks = (int)(grid.x * grid.y);
@@ -552,12 +553,13 @@ extern "C" int gs_loss_bwd(const float *image, int64_t image_stride_h, int64_t i
 {
     if (!image || !gt || !maps || !grad_image) return GS_E_INVALID;
     if (height < kWin || width < kWin) return GS_E_INVALID;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static GsPerDeviceOnce attr_set;
+    int dev = 0;
+    if (attr_set.need(dev)) {
         const cudaError_t e =
             cudaFuncSetAttribute(loss_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kBwdSmem);
         if (e != cudaSuccess) return (int)e;
-        attr_set = true;
+        attr_set.mark(dev);
     }
     const double oh = height - (kWin - 1), ow = width - (kWin - 1);
     const float g_ssim = (float)(-(double)lambda_value / (3.0 * oh * ow));

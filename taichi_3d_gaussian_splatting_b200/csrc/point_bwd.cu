@@ -259,6 +259,10 @@ extern "C" int gs_point_bwd(const float *xyz, const float *features, const int32
     if (!xyz || !features || !object_id || !intrinsics || !q_cam_pc || !t_cam_pc || !t_pc_cam ||
         !ids || !point_in_camera || !splat_grads || !grad_xyz || !grad_features)
         return GS_E_INVALID;
+    // rows move as 16-byte vectors (cp.async in, st / red.global.add.v4 out): a 224-byte row pitch
+    // keeps every row aligned exactly when the base pointers are
+    if (((uintptr_t)features | (uintptr_t)grad_features | (uintptr_t)splat_grads) & 15u) return GS_E_INVALID;
+    if (hook_grad_features && ((uintptr_t)hook_grad_features & 15u)) return GS_E_INVALID;
     PointBwdParams p;
     p.xyz = xyz; p.features = features; p.object_id = object_id; p.intrinsics = intrinsics;
     p.q_cam_pc = q_cam_pc; p.t_cam_pc = t_cam_pc; p.t_pc_cam = t_pc_cam; p.ids = ids; p.m = m;

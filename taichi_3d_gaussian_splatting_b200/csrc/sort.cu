@@ -348,9 +348,10 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
     size_t used = (size_t)kMaxPasses * kRadix * 4 * 2 + 64 + (size_t)num_passes * tiles * kRadix * 4;
     GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, used, st));
 
-    static bool attr_set = false;  // one flag per KeyT instantiation
+    static GsPerDeviceOnce attr_set;  // one per KeyT instantiation
     static bool ballot = true;
-    if (!attr_set) {
+    int dev = 0;
+    if (attr_set.need(dev)) {
         GS_CUDA_TRY(cudaFuncSetAttribute(onesweep_kernel<KeyT, false>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize,
                                          (int)sort_smem(sizeof(KeyT))));
@@ -359,7 +360,7 @@ int sort_impl(const KeyT *keys_first, const int32_t *vals_first, KeyT *keys_a, i
                                          (int)sort_smem(sizeof(KeyT))));
         const char *e = getenv("GS_SORT_RANK");  // tuning knob: "match" or "ballot"
         if (e) ballot = (e[0] == 'b');
-        attr_set = true;
+        attr_set.mark(dev);
     }
 
     if (!ready_hist) {  // else: the producer of the keys counted the digits while writing them

@@ -26,21 +26,24 @@ controller_accumulate_kernel(const int32_t *__restrict__ ids, const long long m,
 {
     const long long i = (long long)blockIdx.x * kThreads + threadIdx.x;
     if (i >= m) return;
-    // ids are the ascending, distinct ids of the visible points (R.py:864): plain read-modify-write
+    // ids are distinct within ONE launch (R.py:864), but launches of different views may run
+    // concurrently on different streams (ViewShardedTrainerStep lanes) and then touch the same
+    // points: every update is a reduction resolved in L2 (RED, no return value), so concurrent
+    // launches cannot lose updates
     const long long id = ids[i];
     const int32_t px = num_affected[i];
     const float mag = magnitude[i];
-    acc_num_in_camera[id] += 1;
-    acc_num_pixels[id] += px;
-    acc_view_grad[id] += mag;
+    atomicAdd(acc_num_in_camera + id, 1);
+    atomicAdd(acc_num_pixels + id, px);
+    atomicAdd(acc_view_grad + id, mag);
     float avg = mag / (float)px;  // 0/0 -> NaN -> 0, as `avg[isnan(avg)] = 0` (AC.py:137-138)
     if (avg != avg) avg = 0.0f;
-    acc_view_grad_avg[id] += avg;
+    atomicAdd(acc_view_grad_avg + id, avg);
     const float gx = grad_xyz[3 * i], gy = grad_xyz[3 * i + 1], gz = grad_xyz[3 * i + 2];
-    acc_pos_grad[3 * id] += gx;
-    acc_pos_grad[3 * id + 1] += gy;
-    acc_pos_grad[3 * id + 2] += gz;
-    acc_pos_grad_norm[id] += sqrtf(gx * gx + gy * gy + gz * gz);
+    atomicAdd(acc_pos_grad + 3 * id, gx);
+    atomicAdd(acc_pos_grad + 3 * id + 1, gy);
+    atomicAdd(acc_pos_grad + 3 * id + 2, gz);
+    atomicAdd(acc_pos_grad_norm + id, sqrtf(gx * gx + gy * gy + gz * gz));
 }
 
 struct AdamScalars {

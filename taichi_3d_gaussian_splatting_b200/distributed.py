@@ -111,7 +111,9 @@ class ViewShardedTrainerStep:
             if self._flat is None or self._flat.numel() != n * 59 or self._flat.device != point_cloud.device:
                 self._flat = torch.empty(n * 59, dtype=torch.float32, device=point_cloud.device)
             self._flat.zero_()
-            gx, gf = self._flat[:3 * n].view(n, 3), self._flat[3 * n:].view(n, 56)
+            # features first: their rows are added as 16-byte vectors and 224 n is a multiple of 16
+            # for every n, 12 n is not
+            gf, gx = self._flat[:56 * n].view(n, 56), self._flat[56 * n:].view(n, 3)
             self.rasteriser.accumulate_gradients_into(gx, gf)
         use_lanes = fused and self.lanes > 1 and point_cloud.is_cuda and len(mine) > 1
         try:

@@ -667,3 +667,129 @@ def test_full_size_properties_of_the_other_baseline_configs(workload):
         assert bool((st.count.to(torch.int64) <= per_pixel).all())
         tiles_per_point = torch.bincount(st.payload.to(torch.int64), minlength=st.m)
         assert torch.equal(tiles_per_point.to(torch.int32), st.buffers.view("num_tiles", st.m).view(-1))
+
+
+def _blend_case_by_hand(seed=0):
+    """A 32x32 image (4 tiles) whose every tile lists every splat, with three kinds of entries the
+    synthetic scenes never produce: (a) conics that are NOT positive definite (an exponent above zero:
+    only the guarded literal path may see it), (b) a NaN opacity (the forward takes such a pair --
+    `alpha < 1/255` is false -- the backward skips it -- `alpha >= 1/255` is false: R.py:451 vs :634),
+    (c) splats whose alpha sits within an ulp of 1/255 on a ring of pixel centres."""
+    rng = np.random.default_rng(seed)
+    W = H = 32
+    m_regular, m_edge = 30, 120
+    uv, conic, alpha, color, z = [], [], [], [], []
+    for _ in range(m_regular):
+        uv.append(rng.uniform(-2, 34, 2))
+        a, c = rng.uniform(0.004, 0.08, 2)
+        b = rng.uniform(-0.9, 0.9) * np.sqrt(a * c)
+        conic.append([a, b, c, rng.uniform(0.6, 1.0)])
+        alpha.append(rng.uniform(0.02, 0.3))
+    for _ in range(m_edge):  # isotropic, centred on a pixel centre: alpha == 1/255 (+- rounding) at distance d
+        centre = rng.integers(4, 28, 2) + 0.5
+        a = rng.uniform(0.01, 0.06)
+        d2 = float(rng.choice([1.0, 2.0, 4.0, 5.0, 8.0, 9.0, 10.0, 13.0]))
+        rescale = rng.uniform(0.7, 1.0)
+        p = np.exp(-0.5 * a * d2) * rescale
+        uv.append(centre)
+        conic.append([a, 0.0, a, rescale])
+        alpha.append(min((1.0 / 255.0) / p * (1.0 + rng.uniform(-2e-7, 2e-7)), 0.95))
+    irregular = [
+        ([10.5, 12.5], [-0.002, 0.0, 0.05, 0.9], 0.5),      # saddle: exponent > 0 away from the centre row
+        ([20.2, 7.7], [0.03, 0.06, 0.03, 0.8], 0.4),        # b^2 > a c
+        ([5.0, 25.0], [-0.001, 0.0005, -0.002, 1.0], 0.3),  # negative definite: alpha grows outwards
+        ([16.0, 16.0], [0.02, 0.0, 0.02, 0.9], np.nan),     # NaN opacity
+    ]
+    for c_uv, c_conic, c_alpha in irregular:
+        uv.append(c_uv); conic.append(c_conic); alpha.append(c_alpha)
+    m = len(uv)
+    uv = np.asarray(uv, np.float32)
+    conic = np.asarray(conic, np.float32)
+    alpha = np.asarray(alpha, np.float32)
+    color = rng.uniform(0.05, 1.0, (m, 3)).astype(np.float32)
+    xyz_cam = np.zeros((m, 3), np.float32)
+    xyz_cam[:, 2] = rng.uniform(1, 20, m).astype(np.float32)
+    order = rng.permutation(m).astype(np.int32)           # one list order, shared by the four tiles
+    payload = np.tile(order, 4)
+    start = (np.arange(4) * m).astype(np.int32)
+    end = start + m
+    records = np.zeros((m, 12), np.float32)
+    records[:, 0:2] = uv
+    records[:, 2:5] = conic[:, 0:3]
+    records[:, 5] = conic[:, 3]
+    records[:, 6] = alpha
+    records[:, 7:10] = color
+    records[:, 10] = xyz_cam[:, 2]
+    return dict(W=W, H=H, m=m, uv=uv, conic=conic, alpha=alpha, color=color, xyz_cam=xyz_cam,
+                payload=payload, start=start, end=end, records=records, first_irregular=m_regular + m_edge)
+
+
+@pytest.mark.parametrize("with_masks", [True, False])
+@pytest.mark.parametrize("persistent", ["1", "0"])
+def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries(
+        oracle32, oracle64, with_masks, persistent, monkeypatch):
+    """gs_blend_fwd + gs_blend_bwd through the C ABI on hand-made records: irregular conics take the
+    guarded literal path in BOTH directions and pairs on the alpha = 1/255 edge are re-decided with
+    the reference's backward arithmetic (R.py:626-669, utils.py:331-345), so num_affected_pixels
+    equals the literal oracle's and the gradients match the fp64 arbiter."""
+    capi = _lib()
+    monkeypatch.setenv("GS_BLEND_PERSISTENT", persistent)
+    c = _blend_case_by_hand()
+    W, H, m = c["W"], c["H"], c["m"]
+    dev = torch.device("cuda")
+    tt = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+    start, end, payload, records = tt(c["start"]), tt(c["end"]), tt(c["payload"]), tt(c["records"])
+    image = torch.empty(H, W, 3, device=dev)
+    depth, acc = torch.empty(H, W, device=dev), torch.empty(H, W, device=dev)
+    last = torch.empty(H, W, dtype=torch.int32, device=dev)
+    count = torch.empty(H, W, dtype=torch.int32, device=dev)
+    k = payload.shape[0]
+    masks = torch.zeros(4 * k, dtype=torch.uint8, device=dev) if with_masks else None
+    st = torch.cuda.current_stream().cuda_stream
+    capi.check(capi.lib.gs_blend_fwd(H, W, start.data_ptr(), end.data_ptr(), payload.data_ptr(),
+                                     records.data_ptr(), image.data_ptr(), depth.data_ptr(), acc.data_ptr(),
+                                     last.data_ptr(), count.data_ptr(), 0,
+                                     masks.data_ptr() if with_masks else None, k, st), "gs_blend_fwd")
+    f = oracle32.blend_fwd(H, W, c["start"], c["end"], c["payload"], c["uv"], c["xyz_cam"], c["conic"],
+                           c["alpha"], c["color"])
+    got = dict(rasterized_image=image.cpu().numpy(), rasterized_depth=depth.cpu().numpy(),
+               pixel_accumulated_alpha=acc.cpu().numpy(),
+               pixel_offset_of_last_effective_point=last.cpu().numpy(),
+               pixel_valid_point_count=count.cpu().numpy())
+    report = util.mismatch_report(f, got, keys=list(got))
+    assert not report, "\n".join(report)
+
+    g = np.random.default_rng(9).uniform(0.1, 1, (H, W, 3)).astype(np.float32)
+    ids = np.arange(m, dtype=np.int32)
+    b32 = oracle32.blend_bwd(H, W, m, c["start"], c["end"], c["payload"], ids, g,
+                             f["pixel_accumulated_alpha"], f["pixel_offset_of_last_effective_point"],
+                             c["uv"], c["conic"], c["alpha"], c["color"])
+    d = lambda a: a.astype(np.float64)
+    b64 = oracle64.blend_bwd(H, W, m, c["start"], c["end"], c["payload"], ids, d(g),
+                             d(f["pixel_accumulated_alpha"]), f["pixel_offset_of_last_effective_point"],
+                             d(c["uv"]), d(c["conic"]), d(c["alpha"]), d(c["color"]))
+    assert np.array_equal(b32["num_affected_pixels"], b64["num_affected_pixels"])
+    splat_grads = torch.zeros(m, 12, device=dev)
+    on_image = torch.empty(H, W, 2, device=dev)
+    capi.check(capi.lib.gs_blend_bwd(H, W, start.data_ptr(), end.data_ptr(), payload.data_ptr(),
+                                     records.data_ptr(), tt(g).data_ptr(), acc.data_ptr(), last.data_ptr(),
+                                     splat_grads.data_ptr(), on_image.data_ptr(),
+                                     masks.data_ptr() if with_masks else None, k, st), "gs_blend_bwd")
+    torch.cuda.synchronize()
+    sg = splat_grads.cpu().numpy()
+    aff = sg[:, 10].astype(np.int64)
+    assert np.array_equal(aff, b32["num_affected_pixels"]), np.nonzero(aff != b32["num_affected_pixels"])
+    # the irregular entries did take part (otherwise this test checks nothing); the NaN-opacity one
+    # is skipped by the backward, as in the reference
+    first = c["first_irregular"]
+    assert (aff[first:first + 3] > 0).all() and aff[first + 3] == 0
+    assert np.isfinite(sg).all()
+    want = np.concatenate([b64["grad_uv"], b64["cov_buf"], b64["color_buf"], b64["grad_logit"][:, None],
+                           b64["magnitude_grad_viewspace"][:, None]], axis=1)
+    l2, mx = util.grad_error(want, sg[:, :10])
+    rows = util.row_error_summary(want, sg[:, :10])
+    print(f"hand-made blend case: rel-l2 {l2:.2e} max-col-norm {mx:.2e} per-row p99.9 {rows['p999']:.1e}")
+    assert l2 <= 1e-4 and mx <= 1e-4
+    l2, mx = util.grad_error(b64["magnitude_grad_viewspace_on_image"].reshape(-1, 2),
+                             on_image.cpu().numpy().reshape(-1, 2))
+    assert l2 <= 1e-4 and mx <= 1e-4

@@ -105,9 +105,16 @@ def test_backward_gradients(case, oracle32, oracle64, band):
                                   b64["grad_pointcloud_features"])):
         l2, mx = util.grad_error(o64, cuda)
         l2o, mxo = util.grad_error(o64, o32)
-        lines.append(f"{name}: cuda vs fp64 oracle rel-l2 {l2:.2e} max-col-norm {mx:.2e}; "
-                     f"fp32 oracle vs fp64 {l2o:.2e} {mxo:.2e}")
+        rows, rows_o = util.row_error_summary(o64, cuda), util.row_error_summary(o64, o32)
+        lines.append(f"{name}: cuda vs fp64 oracle rel-l2 {l2:.2e} max-col-norm {mx:.2e} "
+                     f"per-row p50/p99.9/max {rows['p50']:.1e}/{rows['p999']:.1e}/{rows['max']:.1e}; "
+                     f"fp32 oracle vs fp64 {l2o:.2e} {mxo:.2e} per-row {rows_o['p50']:.1e}/"
+                     f"{rows_o['p999']:.1e}/{rows_o['max']:.1e}")
         assert l2 <= GRAD_RTOL and mx <= GRAD_RTOL, "\n".join(lines)
+        # every row on its own (a row that is small against its column's maximum must be right too):
+        # 99.9 % of the rows within 1e-4 of their own norm; the rest are rows whose terms cancel, where
+        # the reference's own fp32 arithmetic (the literal oracle) is no closer to the fp64 value
+        assert rows["p999"] <= max(GRAD_RTOL, 2.0 * rows_o["p999"]), "\n".join(lines)
     print("\n".join(lines))
     # band mask: coefficients above the band have exactly zero gradient (R.py:1167-1182)
     keep = {0: 1, 1: 4, 2: 9, 3: 16}[band]
@@ -130,23 +137,24 @@ def test_backward_gradients(case, oracle32, oracle64, band):
     assert np.array_equal(h.point_depth.cpu().numpy(), case["ref"]["point_in_camera"][:, 2])
     assert np.array_equal(h.grad_point_in_camera.cpu().numpy(), gx[ids])
     assert np.array_equal(h.grad_pointfeatures_in_camera.cpu().numpy(), gf[ids])
+    # which pairs take part is the reference's fp32 decision (R.py:634): the backward re-decides pairs on
+    # the alpha = 1/255 edge with the literal arithmetic, so the counts are EQUAL to the literal oracle's
+    # (and to the fp64 arbiter's, which takes the same fp32 decisions)
     aff = h.num_affected_pixels.cpu().numpy()
-    aff_ref = b64["num_affected_pixels"]
-    # a pair exactly on the alpha = 1/255 edge may flip between fast and literal arithmetic
-    assert np.abs(aff.astype(np.int64) - aff_ref).sum() <= max(2, 2e-5 * aff_ref.sum())
+    assert np.array_equal(aff, b32["num_affected_pixels"])
+    assert np.array_equal(aff, b64["num_affected_pixels"])
     for name, cuda, o64 in (("grad_viewspace", h.grad_viewspace.cpu().numpy(), b64["grad_uv"][ids]),
                             ("magnitude", h.magnitude_grad_viewspace.cpu().numpy()[:, None],
                              b64["magnitude_grad_viewspace"][ids][:, None])):
         l2, mx = util.grad_error(o64, cuda)
         assert l2 <= GRAD_RTOL and mx <= GRAD_RTOL, f"{name}: {l2:.2e} {mx:.2e}"
-    # the per-pixel map is a sum over one pixel's pairs only: a pair sitting exactly on the
-    # alpha = 1/255 edge (decided by fast arithmetic here, literal arithmetic in the oracle) moves
-    # that single pixel by up to ~1/255 of its sum, so allow 1e-5 of the pixels past the tolerance
+    # the per-pixel map is a sum over one pixel's pairs only; with the same pairs taking part no
+    # pixel is off by a whole pair any more
     cuda = h.magnitude_grad_viewspace_on_image.cpu().numpy().reshape(-1, 2)
     o64 = b64["magnitude_grad_viewspace_on_image"].reshape(-1, 2)
     l2, mx = util.grad_error(o64, cuda)
-    assert l2 <= GRAD_RTOL and mx <= 1e-2, f"on_image: {l2:.2e} {mx:.2e}"
-    assert util.outlier_fraction(o64, cuda, GRAD_RTOL) <= 1e-5
+    assert l2 <= GRAD_RTOL and mx <= GRAD_RTOL, f"on_image: {l2:.2e} {mx:.2e}"
+    assert util.outlier_fraction(o64, cuda, GRAD_RTOL) == 0.0
 
 
 def test_forward_is_deterministic(case):

@@ -179,3 +179,25 @@ def outlier_fraction(ref: np.ndarray, got: np.ndarray, tol: float) -> float:
     col = np.abs(r2).max(axis=0)
     col[col == 0] = 1.0
     return float(((np.abs(r2 - g2) / col) > tol).mean()) if r2.size else 0.0
+
+
+def row_relative_errors(ref: np.ndarray, got: np.ndarray, floor: float = 1e-3) -> np.ndarray:
+    """Per-row relative error ||got_r - ref_r|| / ||ref_r|| over the rows whose reference norm exceeds
+    `floor` x the median norm of the non-zero rows (rows below that are rounding noise of a few pairs).
+    A row that is 100 % wrong shows up here whatever the magnitude of the other rows."""
+    r2 = np.asarray(ref, np.float64).reshape(ref.shape[0], -1)
+    g2 = np.asarray(got, np.float64).reshape(got.shape[0], -1)
+    norms = np.linalg.norm(r2, axis=1)
+    nz = norms[norms > 0]
+    if nz.size == 0:
+        return np.zeros(0)
+    keep = norms > floor * np.median(nz)
+    return np.linalg.norm(g2[keep] - r2[keep], axis=1) / norms[keep]
+
+
+def row_error_summary(ref: np.ndarray, got: np.ndarray) -> dict:
+    e = row_relative_errors(ref, got)
+    if e.size == 0:
+        return dict(rows=0, p50=0.0, p99=0.0, p999=0.0, max=0.0)
+    return dict(rows=int(e.size), p50=float(np.percentile(e, 50)), p99=float(np.percentile(e, 99)),
+                p999=float(np.percentile(e, 99.9)), max=float(e.max()))
