@@ -3,21 +3,29 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
 
-A "step" is one forward+backward of the operator over one camera view of the synthetic workload
-BASELINE.json's metric is quoted on: configs[1] = 1M random Gaussians, SH degree 3, 1920x1088
-(1080p rounded up to whole 16x16 tiles), generated as SURVEY.md section 8(d)
-prescribes.  Views cycle through a small set of nearby camera poses.
+The workload is the configuration BASELINE.json's metric is quoted on: configs[1] = 1M random
+Gaussians, SH degree 3, 1920x1088 (1080p rounded up to whole 16x16 tiles),
+generated as SURVEY.md section 8(d) prescribes.
 
-  value   fwd+bwd iterations/s with every input already resident in HBM (CUDA events)
-  e2e     the same through the public module with HOST inputs: per step the camera pose and the
-          per-pixel loss weights come from pinned host memory (what the reference's trainer
-          uploads per step, Tr.py:149-159: pose + ground-truth image; the Gaussians are
-          nn.Parameters resident on the GPU, Tr.py:65-98) and the scalar loss is read back every
-          step (asynchronous copy into pinned memory, consumed one step later, as a trainer logs it)
-  N > 1   views are sharded over ranks against a replicated cloud; every step ends with an NCCL
-          all-reduce of the N x 59 gradient; weak scaling
+  value        fwd+bwd iterations/s with every input already resident in HBM (CUDA events).  A step is
+               one batch of 8 views per rank, gradients summed in place into one N x 59 buffer, views
+               spread over `lanes` CUDA streams; for N > 1 every step ends with an NCCL all-reduce of
+               that buffer (views sharded over ranks against a replicated cloud).
+  e2e          the same through the public module with HOST inputs: per view the camera pose and the
+               per-pixel target come from pinned host memory (what the reference's trainer uploads per
+               step, Tr.py:149-159) and the scalar loss is read back every step.
+  single_view  what the UNCHANGED reference trainer sees: plain `module(input)` + `loss.backward()`, one
+               view per call, fresh gradient tensors from autograd, one stream, no batch extension.
+  render_e2e   the render half of the metric with the reference's own timing method
+               (benchmark/inference_benchmark.py:13-14,133-160: long warm-up, then 100 timed forwards under
+               no_grad) and what gaussian_point_render.py:100-121 does per frame: pose from the host, the
+               frame converted to 8-bit and copied to host memory.
+  c4           BASELINE.json configs[3] as written: 64 DISTINCT views x 2M Gaussians at 976x544, the 64
+               views of a step split over the ranks (strong scaling), longest-processing-time-first
+               assignment from the previous pass's per-view work, one all-reduce per step, and an on-box
+               check that the reduced gradient equals rank 0 rendering all 64 views alone.
   --impl reference   the CPU oracle (the reference's Taichi kernels cannot run here: no Taichi)
-                     timed on the host cores with OpenMP, same config and metric
+               timed on ALL host cores with OpenMP, same config and metric.
 """
 from __future__ import annotations
 
@@ -43,11 +51,13 @@ WORKLOADS = {
     "c4_2m_976x544": (2_000_000, 976, 544, 0.004, 1004),
     "c5_5m_3840x2160": (5_000_000, 3840, 2160, 0.004, 1006),
 }
-METRIC = "fwd+bwd iters/s"  # BASELINE.json metric, first half; render Mpix/s rides along as render_mpix_per_s
+METRIC = "fwd+bwd iters/s"  # BASELINE.json metric, first half; the render half rides along (render_*)
 NUM_VIEWS = 8
-VIEWS_PER_RANK = 8   # views each rank renders per step (C4: 64 views over 8 GPUs); weak scaling
-FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5, SURVEY.md section 8(d)
+VIEWS_PER_RANK = 8   # views each rank renders per step of the headline leg; weak scaling
+C4_VIEWS = 64        # BASELINE.json configs[3]: 64 camera views per step, split over the ranks
+FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5 (theoretical: 148 SMs x 128 lanes x FMA at 1965 MHz)
 FLOP_PER_PAIR_FWD, FLOP_PER_PAIR_BWD = 28.0, 64.0     # SURVEY.md section 8(d) convention
+RASTER_CFG = (0.8, 1000.0, 100.0)                     # near, far, depth_to_sort_key_scale (R.py:778-780)
 
 
 def parse_args():
@@ -58,6 +68,9 @@ def parse_args():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="c2_1m_1920x1088", choices=list(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-c4", action="store_true", help="skip the 64-view x 2M-point strong-scaling leg")
+    ap.add_argument("--render-frames", type=int, default=100)
+    ap.add_argument("--render-warmup", type=int, default=1000)
     ap.add_argument("--timeline", default=None,
                     help="also write the kernel timeline (name, stream, start, duration; CUPTI through "
                          "torch.profiler) of two untimed resident steps to this JSON file")
@@ -70,7 +83,8 @@ def parse_args():
 
 
 def make_views(num_views: int, seed: int = 5):
-    """Nearby camera poses (T_pointcloud_camera as xyzw quaternion + translation)."""
+    """Nearby camera poses (T_pointcloud_camera as xyzw quaternion + translation): the headline leg
+    keeps every view on the configuration the metric is quoted on."""
     rng = np.random.default_rng(seed)
     q = np.zeros((num_views, 4), np.float32)
     q[:, 3] = 1.0
@@ -79,6 +93,44 @@ def make_views(num_views: int, seed: int = 5):
     t = np.zeros((num_views, 3), np.float32)
     t[1:] = rng.normal(0, 0.05, (num_views - 1, 3))
     return q.astype(np.float32), t.astype(np.float32)
+
+
+def make_views_spread(num_views: int, seed: int = 9):
+    """DISTINCT poses with a real spread (the C4 leg): the camera turns by up to +-20 degrees about its
+    vertical and horizontal axes, rolls by up to +-10, and moves sideways / back and forth inside the
+    near part of the cloud, so that the visible points M and the list entries K differ by well over 2x
+    between views (printed in the bench line)."""
+    rng = np.random.default_rng(seed)
+    q = np.zeros((num_views, 4), np.float32)
+    t = np.zeros((num_views, 3), np.float32)
+    for i in range(num_views):
+        yaw, pitch = np.radians(rng.uniform(-20, 20, 2))
+        roll = np.radians(rng.uniform(-10, 10))
+        shift = [rng.uniform(-0.6, 0.6), rng.uniform(-0.4, 0.4), rng.uniform(-1.5, 3.0)]
+        if i == 0:
+            yaw = pitch = roll = 0.0
+            shift = [0.0, 0.0, 0.0]
+        cy, sy, cp, sp, cr, sr = np.cos(yaw), np.sin(yaw), np.cos(pitch), np.sin(pitch), np.cos(roll), np.sin(roll)
+        Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+        Rx = np.array([[1, 0, 0], [0, cp, -sp], [0, sp, cp]])
+        Rz = np.array([[cr, -sr, 0], [sr, cr, 0], [0, 0, 1]])
+        R = Ry @ Rx @ Rz
+        w = np.sqrt(max(0.0, 1.0 + R[0, 0] + R[1, 1] + R[2, 2])) / 2.0
+        q[i] = [(R[2, 1] - R[1, 2]) / (4 * w), (R[0, 2] - R[2, 0]) / (4 * w), (R[1, 0] - R[0, 1]) / (4 * w), w]
+        t[i] = shift
+    q /= np.linalg.norm(q, axis=1, keepdims=True)
+    return q.astype(np.float32), t.astype(np.float32)
+
+
+def lpt_assignment(costs, world):
+    """Longest-processing-time-first: views by decreasing cost, each to the least loaded rank."""
+    loads = [0.0] * world
+    mine = [[] for _ in range(world)]
+    for v in sorted(range(len(costs)), key=lambda i: -costs[i]):
+        r = min(range(world), key=lambda i: (loads[i], len(mine[i])))
+        mine[r].append(v)
+        loads[r] += costs[v]
+    return mine, loads
 
 
 def peaks():
@@ -170,13 +222,22 @@ def stage_bytes(n, m, k, tiles, hw, info):
         "project_cull_sh": 17 * n + 296 * m,
         **keys,
         "blend_fwd": 48 * k + 28 * hw,
-        "zero_fill": 4 * 59 * n + 48 * m,
+        # what the timed region really zeroes: the M x 12 reduced splat gradients (the N x 59 zero fill of
+        # R.py:1051-1067 is fused away by the in-place accumulation; it is paid once per STEP, outside)
+        "zero_fill": 48 * m,
         "blend_bwd": 44 * k + 28 * hw + 8 * hw + 44 * m,
         "point_bwd": 280 * m + 232 * m,
     }
 
 
-def oracle_step(o, scene, q, t, wt, cfg=(0.8, 1000.0, 100.0), band=None):
+def host_threads() -> int:
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def oracle_step(o, scene, q, t, wt, cfg=RASTER_CFG, band=None):
     """One fwd+bwd of the CPU oracle on one view; returns (seconds, forward dict, backward dict)."""
     if band is not None:
         o.set_tile_row_band(*band)
@@ -195,13 +256,15 @@ def run_reference(args):
     """--impl reference: the CPU restatement of the reference path on the host cores.
 
     The reference's own kernels are Taichi; Taichi is not installable here, so kind = "port".
-    Under torchrun only rank 0 works."""
+    Under torchrun only rank 0 works -- on every host core (torchrun exports OMP_NUM_THREADS=1 to its
+    workers, so the thread count is set explicitly)."""
     if int(os.environ.get("RANK", "0")) != 0:
         return
     from oracle import gs_oracle
     from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
     gs_oracle.build()
     o = gs_oracle.get(False)
+    o.set_num_threads(host_threads())
     n, w, h, sf, seed = WORKLOADS[args.workload]
     scene = make_scene(n, w, h, seed=seed, scale_factor=sf)
     qs, ts = make_views(NUM_VIEWS)
@@ -246,9 +309,84 @@ def run_reference(args):
         "gpu_launches": 0,
         "render_mpix_per_s": None,
         "note": "reference's Taichi kernels unavailable on this box (no taichi wheel); CPU oracle "
-                "= C restatement of the same path, OpenMP over points/tiles",
+                "= C restatement of the same path, OpenMP over points/tiles, one view per step",
     }
     _emit(line)
+
+
+class Rig:
+    """One workload resident on this rank's GPU: the cloud as nn.Parameters, the operator, one flat
+    N x 59 gradient buffer the batch extension sums into, and the lane streams."""
+
+    def __init__(self, torch, impl, dev, workload, lanes):
+        from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+        from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
+        self.torch, self.impl, self.dev = torch, impl, dev
+        self.Ras = impl.GaussianPointCloudRasterisation
+        n, w, h, sf, seed = WORKLOADS[workload]
+        self.n, self.w, self.h, self.workload = n, w, h, workload
+        self.scene = make_scene(n, w, h, seed=seed, scale_factor=sf)
+        self.xyz = torch.nn.Parameter(torch.from_numpy(self.scene.point_cloud).to(dev))
+        self.feat = torch.nn.Parameter(torch.from_numpy(self.scene.point_cloud_features).to(dev))
+        self.inv = torch.from_numpy(self.scene.point_invalid_mask).to(dev)
+        self.oid = torch.from_numpy(self.scene.point_object_id).to(dev)
+        self.cam = CameraInfo(torch.from_numpy(self.scene.camera_intrinsics).to(dev), h, w, 0)
+        self.wt_np = np.random.default_rng(3).uniform(0, 1, (h, w, 3)).astype(np.float32)
+        self.wt_host = torch.from_numpy(self.wt_np).pin_memory()
+        self.wt_dev = self.wt_host.to(dev)
+        self.ras = self.Ras(self.Ras.GaussianPointCloudRasterisationConfig())
+        # features first: their rows are added as 16-byte vectors (224 n is a multiple of 16 for every n)
+        self.flat = torch.zeros(n * 59, dtype=torch.float32, device=dev)
+        self.gf, self.gx = self.flat[:56 * n].view(n, 56), self.flat[56 * n:].view(n, 3)
+        self.lanes = max(1, lanes)
+        self.lane_streams = [torch.cuda.Stream(dev) for _ in range(self.lanes)] if self.lanes > 1 else []
+
+    def batch_mode(self, on: bool):
+        if on:
+            self.ras.accumulate_gradients_into(self.gx, self.gf)
+        else:
+            self.ras.accumulate_gradients_into(None, None)
+
+    def forward(self, q, t):
+        Ras = self.Ras
+        return self.ras(Ras.GaussianPointCloudRasterisationInput(
+            point_cloud=self.xyz, point_cloud_features=self.feat, point_object_id=self.oid,
+            point_invalid_mask=self.inv, camera_info=self.cam, q_pointcloud_camera=q,
+            t_pointcloud_camera=t, color_max_sh_band=3))
+
+    def render_loss(self, q, t, wt):
+        image, _, _ = self.forward(q, t)
+        loss = (image * wt).sum()
+        loss.backward()
+        return loss.detach()
+
+    def run_views(self, count, per_view, use_lanes=True):
+        """`count` views, view j on lane j mod L (the views are independent: their gradients are summed
+        into `flat` by RED either way).  The hot kernels are issue-bound, the key pipeline is latency /
+        HBM bound: views in flight fill each other's idle slots."""
+        torch, dev = self.torch, self.dev
+        cur = torch.cuda.current_stream(dev)
+        if not (use_lanes and self.lane_streams) or count <= 1:
+            total = torch.zeros((), device=dev)
+            for j in range(count):
+                total += per_view(j, cur)
+            return total
+        start = torch.cuda.Event()
+        start.record(cur)
+        totals = []
+        for s in self.lane_streams:
+            s.wait_event(start)
+            with torch.cuda.stream(s):
+                totals.append(torch.zeros((), device=dev))
+        for j in range(count):
+            s = self.lane_streams[j % self.lanes]
+            with torch.cuda.stream(s):
+                totals[j % self.lanes] += per_view(j, s)
+        for s in self.lane_streams:
+            e = torch.cuda.Event()
+            e.record(s)
+            cur.wait_event(e)
+        return torch.stack(totals).sum()
 
 
 def run_b200(args):
@@ -256,10 +394,7 @@ def run_b200(args):
     import torch.distributed as dist
 
     import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
-    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
     from taichi_3d_gaussian_splatting_b200.profiling import StageProfiler
-    from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
-    Ras = impl.GaussianPointCloudRasterisation
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -269,93 +404,62 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    n, w, h, sf, seed = WORKLOADS[args.workload]
-    scene = make_scene(n, w, h, seed=seed, scale_factor=sf)
-    xyz = torch.nn.Parameter(torch.from_numpy(scene.point_cloud).to(dev))
-    feat = torch.nn.Parameter(torch.from_numpy(scene.point_cloud_features).to(dev))
-    inv = torch.from_numpy(scene.point_invalid_mask).to(dev)
-    oid = torch.from_numpy(scene.point_object_id).to(dev)
-    cam = CameraInfo(torch.from_numpy(scene.camera_intrinsics).to(dev), h, w, 0)
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step_fn, steps, warmup):
+        """Device time of exactly `steps` steps: barrier+sync, event pair, barrier+sync; max over ranks."""
+        for i in range(warmup):
+            step_fn(i)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for i in range(steps):
+            step_fn(warmup + i)
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    lanes = max(1, min(args.lanes, VIEWS_PER_RANK))
+    rig = Rig(torch, impl, dev, args.workload, lanes)
+    n, w, h = rig.n, rig.w, rig.h
+    xyz, feat, ras, flat, gx, gf = rig.xyz, rig.feat, rig.ras, rig.flat, rig.gx, rig.gf
     qs_np, ts_np = make_views(NUM_VIEWS)
-    wt_np = np.random.default_rng(3).uniform(0, 1, (h, w, 3)).astype(np.float32)
     # host side of the e2e leg: pinned buffers
     qs_host = torch.from_numpy(qs_np).pin_memory()
     ts_host = torch.from_numpy(ts_np).pin_memory()
-    wt_host = torch.from_numpy(wt_np).pin_memory()
-    # device-resident copies for the kernel-only leg
-    qs_dev, ts_dev, wt_dev = qs_host.to(dev), ts_host.to(dev), wt_host.to(dev)
-    ras = Ras(Ras.GaussianPointCloudRasterisationConfig())
-
-    # A step = one batch of VIEWS_PER_RANK views on every rank (views sharded
-    # over ranks against a replicated cloud): forward+backward of every view, the point gradients
-    # summed into one N x 59 buffer by the backward itself, then ONE all-reduce of that buffer.
-    flat = torch.zeros(n * 59, dtype=torch.float32, device=dev)
-    gf, gx = flat[:56 * n].view(n, 56), flat[56 * n:].view(n, 3)   # 16-byte aligned feature rows for every n
-    ras.accumulate_gradients_into(gx, gf)
+    wt_host, wt_dev = rig.wt_host, rig.wt_dev
+    qs_dev, ts_dev = qs_host.to(dev), ts_host.to(dev)   # device-resident copies for the kernel-only leg
     copy_stream = torch.cuda.Stream(dev)
 
     def view_of(step, j):  # global view index of this rank's j-th view of the step
         return ((step * world + rank) * VIEWS_PER_RANK + j) % NUM_VIEWS
-
-    def render_loss(q, t, wt):
-        image, _, _ = ras(Ras.GaussianPointCloudRasterisationInput(
-            point_cloud=xyz, point_cloud_features=feat, point_object_id=oid,
-            point_invalid_mask=inv, camera_info=cam, q_pointcloud_camera=q,
-            t_pointcloud_camera=t, color_max_sh_band=3))
-        loss = (image * wt).sum()
-        loss.backward()
-        return loss.detach()
 
     def finish_step():
         if world > 1:  # the one exchange step of the path: sum the N x 59 gradient over ranks
             dist.all_reduce(flat)
         xyz.grad, feat.grad = gx, gf
 
-    lanes = max(1, min(args.lanes, VIEWS_PER_RANK))
-    lane_streams = [torch.cuda.Stream(dev) for _ in range(lanes)] if lanes > 1 else []
-
-    def run_views(per_view, use_lanes=True):
-        """The step's views, view j on lane j mod L (the views are independent: their gradients are
-        summed into `flat` by RED either way).  The hot kernels are issue-bound, the key pipeline is
-        latency / HBM bound: two views in flight fill each other's idle slots."""
-        cur = torch.cuda.current_stream(dev)
-        if not (use_lanes and lane_streams):
-            total = torch.zeros((), device=dev)
-            for j in range(VIEWS_PER_RANK):
-                total += per_view(j, cur)
-            return total
-        start = torch.cuda.Event()
-        start.record(cur)
-        totals = []
-        for s in lane_streams:
-            s.wait_event(start)
-            with torch.cuda.stream(s):
-                totals.append(torch.zeros((), device=dev))
-        for j in range(VIEWS_PER_RANK):
-            s = lane_streams[j % lanes]
-            with torch.cuda.stream(s):
-                totals[j % lanes] += per_view(j, s)
-        for s in lane_streams:
-            e = torch.cuda.Event()
-            e.record(s)
-            cur.wait_event(e)
-        return torch.stack(totals).sum()
-
     def resident_view(i):
         def per_view(j, stream):
             v = view_of(i, j)
-            return render_loss(qs_dev[v:v + 1], ts_dev[v:v + 1], wt_dev)
+            return rig.render_loss(qs_dev[v:v + 1], ts_dev[v:v + 1], wt_dev)
         return per_view
 
     def step_resident(i):
         flat.zero_()
-        total = run_views(resident_view(i))
+        total = rig.run_views(VIEWS_PER_RANK, resident_view(i))
         finish_step()
         return total
 
     def step_resident_single_stream(i):  # the instrumented pass: per-stage CUDA events need one stream
         flat.zero_()
-        total = run_views(resident_view(i), use_lanes=False)
+        total = rig.run_views(VIEWS_PER_RANK, resident_view(i), use_lanes=False)
         finish_step()
         return total
 
@@ -397,13 +501,13 @@ def run_b200(args):
                 next_upload[0] += 1
             q, t, wt, ev = uploads.pop(g)
             stream.wait_event(ev)
-            loss = render_loss(q, t, wt)
+            loss = rig.render_loss(q, t, wt)
             done = torch.cuda.Event()
             done.record(stream)
             finished[g] = done
             return loss
 
-        total = run_views(per_view)
+        total = rig.run_views(VIEWS_PER_RANK, per_view)
         finish_step()
         # device -> host read of the step's result, every step, the way a trainer logs a loss: an
         # asynchronous copy into pinned memory, consumed one step later (the host never stalls the
@@ -418,41 +522,40 @@ def run_b200(args):
             loss_log.append(float(loss_host[1 - slot][0]))
         return None
 
+    def step_single_view(i):
+        """One iteration as the unchanged reference trainer runs it (Tr.py:143-184 without the optimiser):
+        gradients set to None, one module call, loss.backward() -- autograd allocates and fills fresh
+        N x 3 / N x 56 gradient tensors, everything on the current stream."""
+        xyz.grad = None
+        feat.grad = None
+        v = view_of(i, 0)
+        return rig.render_loss(qs_dev[v:v + 1], ts_dev[v:v + 1], wt_dev)
+
     def step_render(i):
         v = view_of(i, 0)
         with torch.no_grad():
-            image, _, _ = ras(Ras.GaussianPointCloudRasterisationInput(
-                point_cloud=xyz, point_cloud_features=feat, point_object_id=oid,
-                point_invalid_mask=inv, camera_info=cam, q_pointcloud_camera=qs_dev[v:v + 1],
-                t_pointcloud_camera=ts_dev[v:v + 1], color_max_sh_band=3))
+            image, _, _ = rig.forward(qs_dev[v:v + 1], ts_dev[v:v + 1])
         return image
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
+    frame_host = torch.empty((h, w, 3), dtype=torch.uint8).pin_memory()
 
-    def timed(step_fn, steps, warmup):
-        """Device time of exactly `steps` steps: barrier+sync, event pair, barrier+sync; max over ranks."""
-        for i in range(warmup):
-            step_fn(i)
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for i in range(steps):
-            step_fn(warmup + i)
-        e1.record()
-        barrier()
-        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
-        if world > 1:
-            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        return float(ms.item())
+    def step_render_e2e(i):
+        """gaussian_point_render.py:100-121 per frame: pose from the host, forward under no_grad, the
+        frame clamped, converted to 8 bits and brought to host memory (a blocking copy, as `.cpu()`)."""
+        v = view_of(i, 0)
+        q = qs_host[v:v + 1].to(dev, non_blocking=True)
+        t = ts_host[v:v + 1].to(dev, non_blocking=True)
+        with torch.no_grad():
+            image, _, _ = rig.forward(q, t)
+            frame_host.copy_(torch.clamp(image * 255, 0, 255).byte())
+        return None
 
     warmup = max(args.warmup, 3)
     sampler = ClockSampler(local_rank)
     prof = StageProfiler()
     prio = bool(args.priority_sections) and lanes > 1
     impl.PRIORITY_SECTIONS = prio
+    rig.batch_mode(True)
     timed(step_resident, 0, warmup)            # untimed warm-up (allocator, module load)
     sampler.start()
     ms_resident = timed(step_resident, args.steps, 0)
@@ -468,11 +571,19 @@ def run_b200(args):
     impl.PRIORITY_SECTIONS = prio
     ms_e2e = timed(step_e2e, args.steps, warmup)
     impl.PRIORITY_SECTIONS = False
+    info = dict(ras.last_forward_info)
+    # the drop-in figure and the two render figures (no batch extension, no lanes)
+    rig.batch_mode(False)
+    single_iters = args.steps * VIEWS_PER_RANK
+    ms_single = timed(step_single_view, single_iters, 2 * warmup)
+    xyz.grad = feat.grad = None
     ms_render = timed(step_render, args.steps, warmup)
+    ms_render_e2e = timed(step_render_e2e, args.render_frames, args.render_warmup)
     clocks = sampler.stop()
     if args.timeline and rank == 0:
         from torch.profiler import ProfilerActivity, profile
         impl.PRIORITY_SECTIONS = prio
+        rig.batch_mode(True)
         step_resident(0)
         torch.cuda.synchronize()
         with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tl:
@@ -480,9 +591,18 @@ def run_b200(args):
             step_resident(2)
             torch.cuda.synchronize()
         impl.PRIORITY_SECTIONS = False
+        rig.batch_mode(False)
         tl.export_chrome_trace(args.timeline)
 
-    info = ras.last_forward_info
+    # release the headline workload before the C4 leg allocates its own
+    scene_main = rig.scene
+    xyz.grad = feat.grad = None
+    del rig, xyz, feat, ras, flat, gx, gf, wt_stage, uploads, finished
+    torch.cuda.empty_cache()
+    c4 = None
+    if not args.no_c4:
+        c4 = run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier)
+
     m, k = int(info["num_points_in_camera"]), int(info["num_keys"])
     if rank != 0:
         if world > 1:
@@ -510,7 +630,8 @@ def run_b200(args):
         from oracle import gs_oracle
         gs_oracle.build()
         o = gs_oracle.get(False)
-        dt, f, b = oracle_step(o, scene, qs_np[0:1], ts_np[0:1], wt_np)
+        o.set_num_threads(host_threads())
+        dt, f, b = oracle_step(o, scene_main, qs_np[0:1], ts_np[0:1], wt_host.numpy())
         pairs = {"pairs_fwd": f["pairs_fwd"], "pairs_bwd": b["pairs_bwd"]}
         cpu_baseline = {"value": 1.0 / dt, "unit": "it/s", "cores": o.num_threads(), "kind": "port",
                         "sample": "one full fwd+bwd step of view 0 (whole frame, every stage), "
@@ -525,21 +646,35 @@ def run_b200(args):
     roofline = None
     if dominant is not None:
         d = stages[dominant]
-        roofline = {"kernel": dominant, "bound": "hbm", "achieved": d["gb_s"], "peak": hbm_peak,
-                    "unit": "GB/s", "frac": round(d["gb_s"] / hbm_peak, 4), "traffic": None,
-                    "peak_source": peak_src, "ms_per_launch": d["ms"],
-                    "algorithmic_bytes": d["algorithmic_bytes"]}
+        hbm = {"achieved": d["gb_s"], "peak": hbm_peak, "unit": "GB/s", "frac": round(d["gb_s"] / hbm_peak, 4),
+               "peak_source": peak_src}
+        traffic, traffic_source = None, None
         try:  # measured DRAM bytes per launch of that kernel, from the committed ncu --set full capture
             with open(os.path.join(ROOT, "profiles", "ncu_dram_traffic.json")) as f:
                 entry = json.load(f).get(args.workload, {}).get(dominant)
             if entry:
-                roofline.update(traffic=entry["bytes"], traffic_source=entry["source"])
+                traffic, traffic_source = entry["bytes"], entry["source"]
         except (OSError, ValueError):
             pass
-        if "fp32_tflops" in d:  # the blend kernels are FP32-issue bound, not HBM bound
-            roofline.update(alt_bound="fp32", alt_achieved=d["fp32_tflops"],
-                            alt_peak=round(FP32_PEAK_TFLOPS, 1), alt_unit="TFLOP/s",
-                            alt_frac=d["fp32_frac"])
+        if "fp32_tflops" in d:
+            # the blend kernels are bound by FP32 instruction issue, not by HBM (ncu: issue slots 75-85 %
+            # busy, DRAM 2 %): the binding resource is the primary bound, HBM rides along as alt_*
+            flop = FLOP_PER_PAIR_BWD if dominant == "blend_bwd" else FLOP_PER_PAIR_FWD
+            roofline = {"kernel": dominant, "bound": "fp32", "achieved": d["fp32_tflops"],
+                        "peak": round(FP32_PEAK_TFLOPS, 1), "unit": "TFLOP/s", "frac": d["fp32_frac"],
+                        "traffic": traffic, "traffic_source": traffic_source,
+                        "peak_source": "THEORETICAL: 148 SM x 128 lanes x 2 flop x 1.965 GHz (MEASURED_PEAKS.json "
+                                       f"has no FP32 entry); flops by the SURVEY.md 8(d) convention, {flop:.0f} per "
+                                       "VISITED pair -- the kernel skips the pairs that cannot contribute, so this "
+                                       "is a useful-work rate, not pipe utilisation",
+                        "ms_per_launch": d["ms"], "algorithmic_flop": d["pairs"] * flop,
+                        "algorithmic_bytes": d["algorithmic_bytes"],
+                        "alt_bound": "hbm", "alt_achieved": hbm["achieved"], "alt_peak": hbm["peak"],
+                        "alt_unit": "GB/s", "alt_frac": hbm["frac"], "alt_peak_source": peak_src}
+        else:
+            roofline = {"kernel": dominant, "bound": "hbm", **hbm, "traffic": traffic,
+                        "traffic_source": traffic_source, "ms_per_launch": d["ms"],
+                        "algorithmic_bytes": d["algorithmic_bytes"]}
 
     depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
     if info.get("key_pipeline") == "binned":
@@ -578,14 +713,133 @@ def run_b200(args):
                 "ms_per_step": ms_e2e / args.steps,
                 "loss_readback": "every step, asynchronous copy into pinned memory, read one step later",
                 "losses_read": len(loss_log)},
+        "single_view": {"value": world * single_iters / (ms_single * 1e-3), "unit": "it/s",
+                        "ms_per_iteration": ms_single / single_iters, "iterations": single_iters,
+                        "how": "the unchanged trainer's call pattern: grads set to None, module(input), "
+                               "loss.backward() into fresh autograd-allocated N x 3 / N x 56 tensors, one "
+                               "stream, no accumulate_gradients_into, no lanes" + (
+                                   "; every rank runs its own replica, no exchange" if world > 1 else "")},
         "render_mpix_per_s": world * args.steps * hw / (ms_render * 1e-3) / 1e6,
         "render_ms_per_frame": ms_render / args.steps,
+        "render_e2e": {"mpix_per_s": world * args.render_frames * hw / (ms_render_e2e * 1e-3) / 1e6,
+                       "ms_per_frame": ms_render_e2e / args.render_frames, "frames": args.render_frames,
+                       "warmup_frames": args.render_warmup, "h2d_bytes_per_frame": 28,
+                       "d2h_bytes_per_frame": hw * 3,
+                       "how": "benchmark/inference_benchmark.py's method (long warm-up, then one CUDA-event pair "
+                              "around the timed forwards under no_grad) with gaussian_point_render.py's frame "
+                              "handling: pose uploaded from pinned host memory, clamp(image * 255).byte() copied "
+                              "to host memory with a blocking copy every frame"},
         "gpu_launches": launches_per_step * VIEWS_PER_RANK * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "stages": stages,
+        "c4": c4,
     }
     _emit(line)
     if world > 1:
         dist.destroy_process_group()
+
+
+def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
+    """BASELINE.json configs[3]: 64 distinct views x 2M Gaussians, the views of a step split over the
+    ranks (STRONG scaling: E(G) = T(1, 64 views) / (G T(G, 64 views)))."""
+    name = "c4_2m_976x544"
+    rig = Rig(torch, impl, dev, name, lanes)
+    rig.batch_mode(True)
+    q_np, t_np = make_views_spread(C4_VIEWS)
+    q_dev, t_dev = torch.from_numpy(q_np).to(dev), torch.from_numpy(t_np).to(dev)
+    stats = np.zeros((C4_VIEWS, 2), np.float64)   # per view: M, K of the last recorded pass
+
+    def render_views(mine, record=False):
+        def per_view(j, stream):
+            v = mine[j]
+            loss = rig.render_loss(q_dev[v:v + 1], t_dev[v:v + 1], rig.wt_dev)
+            if record:
+                info = rig.ras.last_forward_info
+                stats[v] = (float(info["num_points_in_camera"]), float(info["num_keys"]))
+            return loss
+        return rig.run_views(len(mine), per_view)
+
+    def step(mine, exchange=True):
+        rig.flat.zero_()
+        total = render_views(mine)
+        if world > 1 and exchange:
+            dist.all_reduce(rig.flat)
+        return total
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps
+
+    # pass 0 (round robin) measures every view's work; from then on the views are dealt out by
+    # longest-processing-time-first on it, the way a trainer would use the previous epoch's numbers
+    round_robin = [list(range(r, C4_VIEWS, world)) for r in range(world)]
+    rig.flat.zero_()
+    render_views(round_robin[rank], record=True)
+    torch.cuda.synchronize()
+    if world > 1:
+        shared = torch.from_numpy(stats).to(dev)
+        dist.all_reduce(shared)
+        stats = shared.cpu().numpy()
+    m_view, k_view = stats[:, 0], stats[:, 1]
+    costs = (k_view + 3.0 * m_view).tolist()        # stage times at C4: ~0.07 ns per list entry, ~0.23 ns per point
+    assignment, loads = lpt_assignment(costs, world)
+    rr_loads = [sum(costs[v] for v in round_robin[r]) for r in range(world)]
+    mine = assignment[rank]
+    steps = max(3, min(args.steps, 6))
+    for _ in range(2):
+        step(mine)
+    ms_step = timed(lambda: step(mine), steps)
+    ms_no_exchange = timed(lambda: step(mine, exchange=False), steps)
+    ms_round_robin = timed(lambda: step(round_robin[rank]), steps) if world > 1 else ms_step
+    ms_exchange_alone = None
+    verify = None
+    if world > 1:
+        ms_exchange_alone = timed(lambda: dist.all_reduce(rig.flat), 5)
+        # on-box check of the exchange: the all-reduced gradient of one step against rank 0 rendering all
+        # 64 views by itself into the same kind of buffer (rows differ only by the order of the additions)
+        step(mine)
+        reduced = rig.flat.clone()
+        result = torch.zeros(3, dtype=torch.float64, device=dev)
+        if rank == 0:
+            step(list(range(C4_VIEWS)), exchange=False)
+            diff = (reduced.double() - rig.flat.double())
+            result[0] = diff.norm() / rig.flat.double().norm()
+            result[1] = diff.abs().max()
+            result[2] = rig.flat.double().abs().max()
+        dist.broadcast(result, 0)
+        verify = {"rel_l2": float(result[0]), "max_abs_diff": float(result[1]), "max_abs": float(result[2]),
+                  "tolerance_rel_l2": 1e-5, "ok": bool(float(result[0]) <= 1e-5),
+                  "what": f"all-reduced N x 59 gradient of one step ({world} ranks) vs rank 0 rendering all "
+                          f"{C4_VIEWS} views alone"}
+    barrier()
+    out = {
+        "workload": name, "points": rig.n, "width": rig.w, "height": rig.h, "views_per_step": C4_VIEWS,
+        "scaling": "strong", "n_gpus": world, "steps": steps, "lanes": lanes,
+        "value": C4_VIEWS / (ms_step * 1e-3), "unit": "it/s", "ms_per_step": ms_step,
+        "ms_per_step_without_exchange": ms_no_exchange,
+        "ms_per_step_round_robin_assignment": ms_round_robin,
+        "exchange_ms_alone": ms_exchange_alone, "exchange_bytes": rig.flat.numel() * 4 if world > 1 else 0,
+        "assignment": "longest-processing-time first on K + 3 M of the previous pass",
+        "rank_load_max_over_mean": max(loads) / (sum(loads) / world),
+        "rank_load_max_over_mean_round_robin": max(rr_loads) / (sum(rr_loads) / world),
+        "views_per_rank": [len(a) for a in assignment],
+        "view_visible_points_min_max": [int(m_view.min()), int(m_view.max())],
+        "view_keys_min_max": [int(k_view.min()), int(k_view.max())],
+        "verify": verify,
+    }
+    rig.batch_mode(False)
+    rig.xyz.grad = rig.feat.grad = None
+    del rig
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():

@@ -32,7 +32,8 @@ extern "C" {
 #define GS_TILE 16          /* R.py:27-28 */
 #define GS_BOUNDARY_TILES 3 /* R.py:26 */
 #define GS_FEATURES 56      /* R.py:208-236 */
-#define GS_RECORD_FLOATS 12 /* packed per-splat record: u v a b c rescale alpha r g b z pad */
+#define GS_RECORD_FLOATS 12 /* packed per-splat record: u v a b c rescale alpha r g b z s; s = log2(rescale
+                             * alpha 255 / (1 + band)), the backward blend's decision band (see gs_blend_bwd) */
 #define GS_GRAD_SLOTS 12    /* per-splat reduced gradients, see gs_blend_bwd */
 
 /* ABI / build identification.  Returns e.g. 100 for the first ABI revision. */
@@ -62,10 +63,16 @@ int gs_inverse_pose(const float *q_pc_cam, const float *t_pc_cam, int n_obj, flo
  *
  * Outputs are in ascending point-id order (decoupled look-back scan), each array
  * sized for n entries; only the first M are written.
- *   ids [n] i32, point_uv [n,2], point_in_camera [n,3], conic [n,4], alpha [n],
- *   color [n,3], radii [n], num_tiles [n] i32, tile_offsets [n] i64 (exclusive scan),
- *   records [n,12] (packed copy for the blend kernels), bbox [n,4] u16 (tu0,tu1,tv0,tv1),
- *   depth_key [n] i32, totals [2] i64 = {M, K}.
+ *   What the path itself reads (required): ids [n] i32, point_in_camera [n,3], records [n,12] (the
+ *   packed per-splat record both blend kernels stage, see GS_RECORD_FLOATS), bbox [n,4] u16
+ *   (tu0,tu1,tv0,tv1), depth_key [n] i32, totals [2] i64 = {M, K}.
+ *   The reference-named per-point buffers (R.py:873-884), each NULLABLE (NULL = not written):
+ *   point_uv [n,2], conic [n,4], alpha [n], color [n,3], radii [n], num_tiles [n] i32 -- the operator
+ *   asks for point_uv / num_tiles only when a backward hook will show them, tests ask for all --
+ *   and tile_offsets [n] i64 (exclusive scan of num_tiles), which only gs_emit_keys reads.  With
+ *   tile_offsets the look-back word packs 27 bits of points and 35 bits of tiles: GS_E_CAPACITY if
+ *   n >= 2^27 or n x (tiles per image) >= 2^35 (a carry could otherwise corrupt the point count).
+ * features: 16-byte aligned (rows are fetched with cp.async.bulk); GS_E_INVALID otherwise.
  * workspace: gs_project_workspace_bytes(n) bytes, contents irrelevant on entry.
  */
 int gs_project_cull_sh(const float *xyz, float *features, const int8_t *invalid_mask,
@@ -161,16 +168,18 @@ int gs_tile_ranges(const int64_t *sorted_keys, int64_t k, int32_t *tile_start, i
  * Forward blend.  Replaces gaussian_point_rasterisation (R.py:318-485).
  * image [H,W,3], depth [H,W], acc_alpha [H,W], last_effective [H,W] i32, valid_count [H,W] i32.
  * Every pixel is written (empty tiles give zeros).  With rgb_only != 0 only image is written.
- * cell_masks (nullable) [4, mask_stride] u8, mask_stride >= k: for every list entry the forward
- * visits, which 8x4-pixel cells of each 8x8 quarter of its tile the splat can reach (plane
- * q = 2 * column + row half; bit 0 = upper cell, bit 1 = lower).  gs_blend_bwd takes the same
- * buffer and then skips its own culling arithmetic; entries the forward never reached (every
- * pixel of the quarter already saturated) are left unwritten and are not read.
+ * What a following gs_blend_bwd needs from the forward (both nullable, both or neither):
+ *   cell_masks [4, mask_stride] u8, mask_stride >= k: for every list entry the forward visits, which
+ *     8x4-pixel cells of each 8x8 quarter of its tile the splat can reach (plane q = 2 * column + row
+ *     half; bit 0 = upper cell, bit 1 = lower); entries the forward never reached (every pixel of the
+ *     quarter already saturated) are left unwritten and are not read;
+ *   quarter_flags [tiles, 4] u8: 1 if the pixels of that 8x8 quarter reach a list entry with an
+ *     irregular conic (not positive definite) or a non-finite field, else 0 (every byte is written).
  */
 int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
                  const int32_t *sorted_payload, const float *records, float *image, float *depth,
                  float *acc_alpha, int32_t *last_effective, int32_t *valid_count, int rgb_only,
-                 uint8_t *cell_masks, int64_t mask_stride, void *stream);
+                 uint8_t *cell_masks, int64_t mask_stride, uint8_t *quarter_flags, void *stream);
 
 /*
  * Backward blend.  Replaces loop 1 of gaussian_point_rasterisation_backward (R.py:531-705).
@@ -178,13 +187,25 @@ int gs_blend_fwd(int height, int width, const int32_t *tile_start, const int32_t
  *   0:duv.u 1:duv.v 2:dcov00 3:dcov01 4:dcov11 5:dr 6:dg 7:db 8:dlogit 9:|duv| 10:#pixels(as float) 11:0
  * map_on_image [H,W,2] gets the per-pixel sum of |duv| (R.py:700-704).  It may be null: the
  * magnitudes (the map and slot 9) are observable only through the reference's backward hook, and
- * a caller without one skips them (slot 9 then stays 0).  cell_masks (nullable): what
- * gs_blend_fwd wrote for the same tile lists.
+ * a caller without one skips them (slot 9 then stays 0).
+ * cell_masks, quarter_flags: REQUIRED, what gs_blend_fwd wrote for the same tile lists (the backward
+ * never redoes the culling arithmetic).  scratch: gs_blend_bwd_scratch_bytes(H, W) bytes, contents
+ * irrelevant on entry (one flag byte per pixel: which pixels the literal pass re-does).
+ * records: as written by gs_project_cull_sh, INCLUDING the 12th float s of every record: with
+ *   rho = |b| / sqrt(a c), tau = max(2 ln(255 rescale alpha), 0),
+ *   band = min(3e-6 + 6e-7 tau (1 + rho) / (1 - rho), 0.02),   s = log2(255 rescale alpha / (1 + band))
+ * (0 for records that are irregular or can never reach alpha = 1/255).  band bounds the relative difference
+ * between this kernel's fast alpha and the reference's fp32 alpha near the threshold; pairs inside it
+ * are re-decided with the reference's arithmetic.
+ * Which (pixel, entry) pairs take part is decided as the reference decides it (alpha >= 1/255 on its
+ * fp32 backward arithmetic, R.py:626-634): slot 10 equals the reference's in_camera_num_affected_pixels.
  */
+int64_t gs_blend_bwd_scratch_bytes(int height, int width);
 int gs_blend_bwd(int height, int width, const int32_t *tile_start, const int32_t *tile_end,
                  const int32_t *sorted_payload, const float *records, const float *image_grad,
                  const float *acc_alpha, const int32_t *last_effective, float *splat_grads,
-                 float *map_on_image, const uint8_t *cell_masks, int64_t mask_stride, void *stream);
+                 float *map_on_image, const uint8_t *cell_masks, int64_t mask_stride,
+                 const uint8_t *quarter_flags, void *scratch, void *stream);
 
 /*
  * Per-point chain rule + SH band mask + factor scaling.  Replaces loop 2 of the backward kernel

@@ -115,6 +115,16 @@ static int g_band_begin = -1, g_band_end = -1;
 void FN(set_tile_row_band)(int begin, int end) { g_band_begin = begin; g_band_end = end; }
 static int tile_in_band(int tile_v) { return g_band_begin < 0 || (tile_v >= g_band_begin && tile_v < g_band_end); }
 
+/* torchrun exports OMP_NUM_THREADS=1 to its workers: the CPU arm sets its thread count itself */
+void FN(set_num_threads)(int threads)
+{
+#ifdef _OPENMP
+    if (threads > 0) omp_set_num_threads(threads);
+#else
+    (void)threads;
+#endif
+}
+
 int FN(num_threads)(void)
 {
 #ifdef _OPENMP

@@ -64,6 +64,10 @@ class OracleLib:
     def num_threads(self) -> int:
         return int(self.fn("num_threads", C.c_int)())
 
+    def set_num_threads(self, threads: int) -> None:
+        """OpenMP threads of the following calls (a launcher may have exported OMP_NUM_THREADS=1)."""
+        self.fn("set_num_threads")(C.c_int(int(threads)))
+
     def set_tile_row_band(self, begin: int = -1, end: int = -1) -> None:
         """Restrict both blend loops to tile rows [begin, end) (bench.py's bounded CPU sample)."""
         self.fn("set_tile_row_band")(C.c_int(begin), C.c_int(end))

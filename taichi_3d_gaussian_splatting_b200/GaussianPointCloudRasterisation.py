@@ -47,10 +47,6 @@ _GRAD_SLOTS = 12
 # tile ranges.  Falls back to "depth_first" when the image has more than 256 tile columns or rows.
 KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "binned")
 
-# the backward blend reuses the culling bits the forward blend computed (4 bytes per list entry kept
-# between forward and backward); 0 makes it recompute them
-REUSE_CELL_MASKS = os.environ.get("GS_REUSE_CELL_MASKS", "1") != "0"
-
 # operator calls made through this module since import (acceptance tests check that the reference's
 # unchanged callers really ran THIS code)
 CALL_COUNTS = {"forward": 0, "backward": 0, "hook": 0}
@@ -100,7 +96,11 @@ def _align(x: int, a: int = 256) -> int:
 
 
 class _PointBuffers:
-    """Carves the per-visible-point arrays (capacity n rows) out of one byte buffer."""
+    """Carves the per-visible-point arrays (capacity n rows) out of one byte buffer.
+
+    CORE is what the path itself reads (76 bytes per point); HOOK the two reference-named buffers a
+    backward hook shows (R.py:1127-1142); DEBUG the remaining reference-named buffers (R.py:873-884),
+    which nothing but tests looks at; OFFSETS the scan the literal key pipeline reads."""
 
     FIELDS = (  # name, dtype, columns
         ("ids", torch.int32, 1),
@@ -116,19 +116,37 @@ class _PointBuffers:
         ("bbox", torch.int16, 4),
         ("depth_key", torch.int32, 1),
     )
+    CORE = ("ids", "point_in_camera", "records", "bbox", "depth_key")
+    HOOK = ("point_uv", "num_tiles")
+    DEBUG = ("conic", "alpha", "color", "radii")
+    OFFSETS = ("tile_offsets",)
 
-    def __init__(self, n: int, device: torch.device):
+    def __init__(self, n: int, device: torch.device, hook: bool = False, debug: bool = False,
+                 offsets: bool = False):
         self.n = n
+        wanted = set(self.CORE)
+        if hook or debug:
+            wanted |= set(self.HOOK)
+        if debug:
+            wanted |= set(self.DEBUG)
+        if offsets:
+            wanted |= set(self.OFFSETS)
         self.offsets: Dict[str, int] = {}
         off = 0
         for name, dtype, cols in self.FIELDS:
+            if name not in wanted:
+                continue
             self.offsets[name] = off
             off = _align(off + max(n, 1) * cols * torch.empty((), dtype=dtype).element_size())
         self.storage = torch.empty(off, dtype=torch.uint8, device=device)
         self.base = self.storage.data_ptr()
 
-    def ptr(self, name: str) -> int:
-        return self.base + self.offsets[name]
+    def has(self, name: str) -> bool:
+        return name in self.offsets
+
+    def ptr(self, name: str) -> Optional[int]:
+        """Device address of the array, or None (a NULL pointer: not produced) if it was not asked for."""
+        return self.base + self.offsets[name] if name in self.offsets else None
 
     def view(self, name: str, rows: int) -> torch.Tensor:
         for fname, dtype, cols in self.FIELDS:
@@ -234,7 +252,8 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                 out = _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask,
                                     point_object_id, q_pointcloud_camera, t_pointcloud_camera,
                                     camera_info,
-                                    keep_cell_masks=ctx.needs_input_grad[0] or ctx.needs_input_grad[1])
+                                    keep_cell_masks=ctx.needs_input_grad[0] or ctx.needs_input_grad[1],
+                                    hook_outputs=backward_valid_point_hook is not None)
                 outer.last_forward_info = out.info
                 ctx.set_materialize_grads(False)
                 ctx.camera_info = camera_info
@@ -332,7 +351,8 @@ class _ForwardState:
     """Everything the backward needs, plus handles a test can read every stage from."""
     __slots__ = ("n", "m", "k", "width", "height", "buffers", "payload", "keys", "tile_start",
                  "tile_end", "image", "depth", "count", "acc_alpha", "last", "q_cam", "t_cam",
-                 "intrinsics", "info", "unsorted_keys", "unsorted_payload", "tile_ids", "cell_masks")
+                 "intrinsics", "info", "unsorted_keys", "unsorted_payload", "tile_ids", "cell_masks",
+                 "quarter_flags")
 
     def sorted_keys(self) -> torch.Tensor:
         """The reference's sorted 64-bit keys (point_in_camera_sort_key, R.py:947) of this forward."""
@@ -374,7 +394,12 @@ def _check_inputs(pointcloud, features, invalid_mask, object_id, q, t, intrinsic
 
 def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, point_object_id,
                   q_pointcloud_camera, t_pointcloud_camera, camera_info,
-                  keep_unsorted: bool = False, keep_cell_masks: bool = False) -> _ForwardState:
+                  keep_unsorted: bool = False, keep_cell_masks: bool = False,
+                  hook_outputs: bool = False, debug_outputs: bool = False,
+                  offsets_output: bool = False) -> _ForwardState:
+    """hook_outputs: also produce point_uv / num_overlap_tiles (a backward hook will show them);
+    debug_outputs: every reference-named per-point buffer (tests); offsets_output: the exclusive scan
+    of the tile counts even when the key pipeline in use does not read it (tests)."""
     CALL_COUNTS["forward"] += 1
     dev = pointcloud.device
     intrinsics = camera_info.camera_intrinsics
@@ -406,7 +431,16 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     _capi.check(_lib.gs_inverse_pose(q_pc.data_ptr(), t_pc.data_ptr(), n_obj, st.q_cam.data_ptr(),
                                      st.t_cam.data_ptr(), stream), "gs_inverse_pose")
 
-    buf = _PointBuffers(n, dev)
+    num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
+    depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
+                                          float(cfg.depth_to_sort_key_scale), num_tiles)
+    depth_first = KEY_PIPELINE in ("depth_first", "binned") and depth_bits <= 31
+    binned = (depth_first and KEY_PIPELINE == "binned" and W // TILE_WIDTH <= 256
+              and H // TILE_HEIGHT <= 256)
+    # the per-point scan of the tile counts is read by the literal key emission only (binned falls back
+    # to depth_first, never to literal)
+    buf = _PointBuffers(n, dev, hook=hook_outputs, debug=debug_outputs,
+                        offsets=offsets_output or not depth_first)
     st.buffers = buf
     totals = torch.empty(2, dtype=torch.int64, device=dev)
     ws = torch.empty(max(int(_lib.gs_project_workspace_bytes(n)), 16), dtype=torch.uint8, device=dev)
@@ -421,12 +455,6 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     _mark("project_cull_sh")
     after_project = torch.cuda.Event()
     after_project.record(s_small)
-    num_tiles = (W // TILE_WIDTH) * (H // TILE_HEIGHT)
-    depth_bits, tile_bits = sort_key_bits(float(cfg.near_plane), float(cfg.far_plane),
-                                          float(cfg.depth_to_sort_key_scale), num_tiles)
-    depth_first = KEY_PIPELINE in ("depth_first", "binned") and depth_bits <= 31
-    binned = (depth_first and KEY_PIPELINE == "binned" and W // TILE_WIDTH <= 256
-              and H // TILE_HEIGHT <= 256)
     order = None
     if depth_first and n > 0:
         # The argsort of the visible points by depth needs M only on the device: enqueue it for
@@ -534,16 +562,21 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                                         st.tile_start.data_ptr(), st.tile_end.data_ptr(), num_tiles,
                                         stream), "gs_tile_ranges")
         _mark("tile_ranges")
-    # the forward's exact culling bits per (list entry, 8x4 cell), kept for the backward blend so that
-    # it does not redo the arithmetic: four planes (one per 8x8 quarter of a tile) of k bytes
-    st.cell_masks = torch.empty(4 * k, dtype=torch.uint8, device=dev) if (keep_cell_masks and REUSE_CELL_MASKS and k > 0) else None
+    # what the backward blend takes over from the forward blend instead of redoing the arithmetic: the
+    # exact culling bits per (list entry, 8x4 cell) -- four planes (one per 8x8 quarter of a tile) of k
+    # bytes -- and one flag per quarter (does it reach an entry with an irregular conic)
+    if keep_cell_masks:
+        st.cell_masks = torch.empty(max(4 * k, 1), dtype=torch.uint8, device=dev)
+        st.quarter_flags = torch.empty(4 * num_tiles, dtype=torch.uint8, device=dev)
+    else:
+        st.cell_masks = st.quarter_flags = None
     _hand_over(s_small, s_big)
     stream = s_big.cuda_stream
     _capi.check(_lib.gs_blend_fwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if k > 0 else None, buf.ptr("records"),
                                   st.image.data_ptr(), st.depth.data_ptr(), st.acc_alpha.data_ptr(),
                                   st.last.data_ptr(), st.count.data_ptr(), int(rgb_only),
-                                  _ptr(st.cell_masks), k, stream),
+                                  _ptr(st.cell_masks), k, _ptr(st.quarter_flags), stream),
                 "gs_blend_fwd")
     _mark("blend_fwd")
     st.info = dict(num_points=n, num_points_in_camera=m, num_keys=k, depth_bits=depth_bits,
@@ -578,11 +611,15 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     on_image = torch.empty(H, W, 2, dtype=torch.float32, device=dev) if want_hook else None
     splat_grads = torch.zeros(max(m, 1), _GRAD_SLOTS, dtype=torch.float32, device=dev)
     buf = st.buffers
+    if st.cell_masks is None:
+        raise _capi.GsError("backward of a forward that ran without gradient tracking (no culling bits kept)")
+    scratch = torch.empty(max(int(_lib.gs_blend_bwd_scratch_bytes(H, W)), 1), dtype=torch.uint8, device=dev)
     _mark("zero_fill")
     _capi.check(_lib.gs_blend_bwd(H, W, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
                                   st.payload.data_ptr() if st.k > 0 else None, buf.ptr("records"),
                                   g_img.data_ptr(), st.acc_alpha.data_ptr(), st.last.data_ptr(),
-                                  splat_grads.data_ptr(), _ptr(on_image), _ptr(st.cell_masks), st.k, stream),
+                                  splat_grads.data_ptr(), _ptr(on_image), st.cell_masks.data_ptr(), st.k,
+                                  st.quarter_flags.data_ptr(), scratch.data_ptr(), stream),
                 "gs_blend_bwd")
     _mark("blend_bwd")
     h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None

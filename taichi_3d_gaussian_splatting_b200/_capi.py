@@ -12,9 +12,9 @@ import os
 from . import build as _build
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libgs_b200.so")
+LIB_PATH = _build.LIB
 
-ABI_VERSION = 108
+ABI_VERSION = 109
 
 _p = C.c_void_p
 _i = C.c_int
@@ -43,8 +43,9 @@ SIGNATURES = {
     "gs_emit_keys": (_i, [_p, _p, _p, _l, _l, _i, _p, _p, _p]),
     "gs_sort_pairs": (_i, [_p, _p, _p, _p, _l, _i, _i, _p, C.POINTER(C.c_int), _p]),
     "gs_tile_ranges": (_i, [_p, _l, _p, _p, _i, _p]),
-    "gs_blend_fwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p]),
-    "gs_blend_bwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _p]),
+    "gs_blend_fwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p, _p]),
+    "gs_blend_bwd_scratch_bytes": (_l, [_i, _i]),
+    "gs_blend_bwd": (_i, [_i, _i, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _l, _p, _p, _p]),
     "gs_point_bwd": (_i, [_p, _p, _p, _p, _p, _p, _p, _i, _p, _l, _p, _p, _i, _f, _f, _f, _f, _f,
                           _p, _p, _p, _p, _p, _p, _p, _i, _p]),
     "gs_loss_workspace_bytes": (_l, [_i, _i]),

@@ -15,7 +15,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 INCLUDE = os.path.join(os.path.dirname(HERE), "include")
-LIB = os.path.join(HERE, "libgs_b200.so")
+# GS_B200_LIB_NAME: another file name for the library (tuning experiments build variants side by side)
+LIB = os.path.join(HERE, os.environ.get("GS_B200_LIB_NAME", "libgs_b200.so"))
 
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-I", INCLUDE, "-I", CSRC]
@@ -53,7 +54,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not _stale():
         return LIB
     nvcc = nvcc_path()
-    objdir = os.path.join(HERE, "build")
+    objdir = os.path.join(HERE, "build", os.path.basename(LIB).replace(".so", "") if "GS_B200_LIB_NAME" in os.environ else "")
     os.makedirs(objdir, exist_ok=True)
     procs = []
     for unit, extra in UNITS.items():

@@ -1,30 +1,43 @@
 // blend_bwd.cu -- reverse-order blend backward (reference R.py:531-705, utils.py:331-348).
 //
-// Fast-fp32 profile (FMA contraction, ex2.approx, rcp.approx): gradients are compared with the
-// oracle at 1e-4 relative, the atomic summation order differs from the reference anyway.
-// The DECISION whether a (pixel, entry) pair takes part (alpha >= 1/255, R.py:634) is nevertheless
-// the reference's: a pair whose fast alpha lies within a per-entry error band of 1/255, and every
-// pair of an entry with an irregular conic / non-finite field, is re-decided with the reference's
-// backward arithmetic in literal fp32 (literal_alpha below = utils.py:331-345 with gs_expf), so
-// the set of contributing pairs -- num_affected_pixels -- equals the literal-fp32 oracle's exactly.
+// Two kernels:
 //
-// Instruction-issue bound like the forward blend, and laid out the same way: one WARP owns a
+// blend_bwd_kernel (hot).  Fast-fp32 profile (FMA contraction, ex2.approx, rcp.approx): gradients are
+// compared with the oracle at 1e-4 relative, the atomic summation order differs from the reference
+// anyway.  Instruction-issue bound like the forward blend, and laid out the same way: one WARP owns a
 // column of kCells cells of 8x4 pixels (kCells = 4: an 8x16 half tile); lane l owns pixel
-// (l % 8, l / 8) of every cell.  The tile's list is walked from max-over-pixels(last effective
-// index) down to the tile start (entries past that maximum are skipped by every pixel in the
-// reference too, R.py:609-610) in batches of 32: lane l stages entry l of the batch (records
-// prefetched one batch ahead into registers) and computes a kCells-bit mask -- bit j is set only
-// if the splat can reach alpha >= 1/255 on some pixel centre of cell j (gs_cell_mask) and some
-// pixel of the cell still has that entry before its last effective index.  The warp then visits
-// only (entry, cell) combinations whose bit is set, sums the per-pixel gradient terms over its
-// cells in registers, and reduces them across the warp once per (warp, entry) with a
-// recursive-halving butterfly over 10 values (12 shuffles), followed by three 16-byte vector
-// reductions into the [M,12] splat-gradient buffer.  The reference issues 11 global atomics per
-// (pixel, splat) pair (R.py:674-696).
+// (l % 8, l / 8) of every cell.  The tile's list is walked from max-over-pixels(last effective index)
+// down to the tile start (entries past that maximum are skipped by every pixel in the reference too,
+// R.py:609-610) in batches of 32: lane l stages entry l of the batch (records prefetched one batch
+// ahead into registers) together with the culling bits the FORWARD blend stored for it (which 8x4 cells
+// the splat can reach at all).  The warp then visits only (entry, cell) combinations whose bit is set,
+// sums the per-pixel gradient terms over its cells in registers, and reduces them across the warp once
+// per (warp, entry) with a recursive-halving butterfly over 10 values (12 shuffles), followed by three
+// 16-byte vector reductions into the [M,12] splat-gradient buffer.  The reference issues 11 global
+// atomics per (pixel, splat) pair (R.py:674-696).  Per pixel the three colour channels are folded: with
+// cg = colour . dL/dpixel, the reference's sum_c (colour_c T - w_c / (1 - alpha)) dL/dpixel_c equals
+// T cg - wg / (1 - alpha), where wg = sum over the entries behind of (alpha T) cg.
 //
-// Per pixel the three colour channels are folded: with cg = colour . dL/dpixel, the reference's
-// sum_c (colour_c T - w_c / (1 - alpha)) dL/dpixel_c equals T cg - wg / (1 - alpha), where
-// wg = sum over the entries behind of (alpha T) cg, so one accumulator replaces three.
+// The hot loop is kept SMALL on purpose (it is sensitive to its instruction footprint: every variant
+// that put the rare cases below inside it, inline or as a call, cost 8-25 %).  What it does not do:
+//
+//   * Which pairs take part is the reference's decision `alpha >= 1/255` (R.py:634) on ITS fp32
+//     arithmetic.  The hot loop takes every pair whose fast alpha is >= lo = (1 - band)/255 and only
+//     REMEMBERS, per pixel, whether it met a pair below hi = (1 + band)/255, i.e. one whose literal
+//     alpha may fall on the other side (band: gs_decision_band_log2() in gs_common.cuh, a per-splat
+//     bound of the difference between the two arithmetics, computed by the projection kernel and
+//     carried in the record's 12th float; ~1e-5 of the contributing pairs).  That costs the hot
+//     block ONE instruction: alpha is formed as 2^x' hi with x' = log2(alpha / hi), and the sign bits
+//     of the x' of the pairs taken are OR-ed together.
+//   * Quarters whose list holds an irregular entry (conic not positive definite, non-finite field:
+//     the forward blend flags them) are not processed here at all.
+//
+// blend_bwd_fixup_kernel (cold, one warp per flagged pixel).  Re-does the flagged pixels exactly as the
+// reference does -- every pair decided and formed with literal_alpha(), the reference's backward
+// arithmetic in literal fp32 with the guarded exp -- and, for a pixel the hot kernel did process, takes
+// the hot kernel's own contribution for that pixel out again by replaying its arithmetic with the
+// opposite sign.  The set of contributing pairs (num_affected_pixels) therefore EQUALS the literal
+// oracle's, irregular conics included.
 #include <cstdlib>
 
 #include "gs_common.cuh"
@@ -32,6 +45,9 @@
 namespace {
 
 constexpr int kBatch = 32;
+constexpr float kAlphaMin = 1.0f / 255.0f;
+// fix list: scratch = {unsigned count; unsigned entries[H * W]}, entry = pixel index | kFixWholeBit
+constexpr unsigned kFixWholeBit = 1u << 31;
 
 __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d)
 {
@@ -60,6 +76,37 @@ __device__ __forceinline__ float fast_sqrt(float x)
     return y;
 }
 
+// Per-entry constants of the decision band.  The record's 12th float, written by gs_project_cull_sh, is
+// s = log2(peak / hi) with peak = rescale * opacity and hi = (1 + band) / 255: the upper edge of the band
+// inside which the fast alpha and the literal one may fall on different sides of 1/255.  From it:
+//   hi  = peak 2^-s                      (so that alpha = 2^x' hi with x' = log2(alpha / hi))
+//   xlo = log2(lo / hi), lo = (1 - band)/255, i.e. ~ -2 band log2(e) (rounded away from zero)
+// A pair is TAKEN iff x' >= xlo and AMBIGUOUS iff it is taken and x' < 0 (its sign bit).  The lane that
+// stages an entry computes (hi, xlo) once and passes them to the visits in the two record slots the
+// backward does not need (rescale and depth).
+struct BandConsts {
+    float hi, xlo;
+};
+__device__ __forceinline__ BandConsts band_consts(float peak, float s)
+{
+    BandConsts k;
+    k.hi = peak * fast_ex2(-s);
+    k.xlo = fmaf(k.hi, -2.8856f * 255.0f, 2.8856f - 4e-6f);  // -2.8856 (255 hi - 1) = -2.8856 band, minus slack
+    return k;
+}
+
+// alpha of a pair in the fast profile, as (x', alpha); v = conic d comes back for the gradient terms.
+// One function for the hot kernel and for the fix-up's replay of it: both must take the same decisions.
+__device__ __forceinline__ float fast_alpha(float dx, float dy, float adx, float bdx, float b, float c,
+                                            float s, float hi, float &v0, float &v1, float &xp)
+{
+    v0 = fmaf(b, dy, adx);
+    v1 = fmaf(c, dy, bdx);
+    const float quad = fmaf(dy, v1, dx * v0);
+    xp = fmaf(quad, -0.72134752044448170368f, s);
+    return fast_ex2(xp) * hi;
+}
+
 // alpha of a pair exactly as the reference's backward forms it (utils.py:331-345, R.py:628-631) in
 // literal fp32: v = conic d (Taichi's mat @ vec: a[i,0] b[0] + a[i,1] b[1]), quad = d . v,
 // p = exp(-0.5 quad) rescale, alpha = p opacity.  _rn intrinsics are never contracted.
@@ -70,18 +117,6 @@ __device__ __forceinline__ float literal_alpha(float dx, float dy, float a, floa
     const float v1 = __fadd_rn(__fmul_rn(b, dx), __fmul_rn(c, dy));
     const float quad = __fadd_rn(__fmul_rn(dx, v0), __fmul_rn(dy, v1));
     return __fmul_rn(__fmul_rn(gs_expf(__fmul_rn(-0.5f, quad)), rescale), opacity);
-}
-
-// Relative half-width of the band around 1/255 inside which the fast alpha (FMA-contracted quadratic
-// form, ex2.approx, pre-multiplied peak) and the literal one may fall on different sides.  The two
-// exponents differ by at most ~5e-7 of the sum P of the magnitudes of the quadratic form's terms, and
-// P <= quad (1 + rho) / (1 - rho) <= 4 quad a c / (a c - b^2) with rho = |b| / sqrt(a c); near the
-// threshold quad = 2 ln(255 peak) <= 11.1.  The constants leave a factor > 4 of slack; the exp
-// approximations and the products add < 2e-6.
-__device__ __forceinline__ float decision_band(float a, float b, float c)
-{
-    const float ac = a * c;
-    return fmaf(2.7e-5f, ac * fast_rcp(ac - b * b), 3e-6f);
 }
 
 // Sum 10 per-lane values over the 32 lanes of a warp with 12 shuffles.  On return v[0] of lane L
@@ -131,14 +166,25 @@ __device__ __forceinline__ int reduced_slot(int lane)
     return 5 * (lane >> 4) + 3 * b3 + 2 * b2 + b1;
 }
 
-template <int kCells, bool kMagnitude, bool kMasks>
-__global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)))
+// resident warps per SM the kernel is compiled for: 20 (<= 96 registers; the product path, no
+// magnitudes) or 16 when the |duv| magnitudes are accumulated too (they need 8 more registers)
+#ifndef GS_BWD_MIN_WARPS
+#define GS_BWD_MIN_WARPS 20
+#endif
+constexpr int bwd_min_ctas(int cells, bool magnitude)
+{
+    return (magnitude ? 16 : GS_BWD_MIN_WARPS) / (kTilePixels / (cells * 32));
+}
+
+template <int kCells, bool kMagnitude>
+__global__ void __launch_bounds__(32 * (kTilePixels / (kCells * 32)), bwd_min_ctas(kCells, kMagnitude))
 blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
                  const float4 *__restrict__ records, const float *__restrict__ image_grad,
                  const float *__restrict__ acc_alpha, const int32_t *__restrict__ last_effective,
                  float *__restrict__ splat_grads, float *__restrict__ map_on_image,
                  const uint8_t *__restrict__ cell_masks, const long long mask_stride,
+                 const uint8_t *__restrict__ quarter_flags, unsigned *__restrict__ fix_list,
                  GsWorkCounter *__restrict__ work, const unsigned num_units)
 {
     constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile = units per tile
@@ -166,31 +212,40 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
     const int pu = col0 + (lane & 7);
     const int pv0 = row0 + (lane >> 3);
     const float fx = (float)pu + 0.5f, fy0 = (float)pv0 + 0.5f;
-    const float x_first = (float)col0 + 0.5f, y_first = (float)row0 + 0.5f;
     const int start = tile_start[tile], end = tile_end[tile];
+    const int q0 = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * (kCells / 2);  // first 8x8 quarter
+
+    // a quarter with an irregular entry in reach is left, whole, to the literal pass
+    unsigned whole = 0u;  // bit h: quarter q0 + h
+#pragma unroll
+    for (int h = 0; h < kCells / 2; ++h) whole |= (quarter_flags[4 * tile + q0 + h] ? 1u : 0u) << h;
 
     float T[kCells], wg[kCells], g0[kCells], g1[kCells], g2[kCells];
     float tot0[kCells], tot1[kCells];
     int last[kCells], cell_last[kCells];
-    int hi = start;
+    int hi_index = start;
 #pragma unroll
     for (int j = 0; j < kCells; ++j) {
         const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
         last[j] = (end > start) ? min(last_effective[px], end) : start;
+        if ((whole >> (j / 2)) & 1u) {
+            fix_list[1u + atomicAdd(fix_list, 1u)] = (unsigned)px | kFixWholeBit;
+            last[j] = start;  // nothing of this cell is processed here
+        }
         T[j] = 1.0f - acc_alpha[px];
         g0[j] = image_grad[3 * px];
         g1[j] = image_grad[3 * px + 1];
         g2[j] = image_grad[3 * px + 2];
         wg[j] = tot0[j] = tot1[j] = 0.f;
         cell_last[j] = __reduce_max_sync(0xffffffffu, last[j]);
-        hi = max(hi, cell_last[j]);
+        hi_index = max(hi_index, cell_last[j]);
     }
 
     // software pipeline: records of the next batch in registers, payload two batches ahead
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
     int g_cur = 0, g_next = 0;
     {
-        const int i = hi - 1 - lane;
+        const int i = hi_index - 1 - lane;
         if (i >= start) {
             g_cur = __ldg(payload + i);
             const float4 *src = records + (size_t)3 * g_cur;
@@ -199,40 +254,31 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
     }
 
-    for (int top = hi; top > start; top -= kBatch) {
+    for (int top = hi_index; top > start; top -= kBatch) {
         // ---- stage: lane l holds entry top-1-l (reverse order) ---------------------------------
         const int my_i = top - 1 - lane;
         const int my_g = g_cur;
-        unsigned my_mask = 0u;  // cell bits | kCellMaskIrregular
+        unsigned my_mask = 0u;
         if (my_i >= start) {
             unsigned live = 0u;
 #pragma unroll
             for (int j = 0; j < kCells; ++j) live |= (my_i < cell_last[j] ? 1u : 0u) << j;
             if (live) {
+                // the forward's culling bits for these cells: plane q of the tile's 8x8 quarters, two
+                // bits (upper / lower 8x4 cell) per entry
                 unsigned m = 0u;
-                if (kMasks) {
-                    // the forward's culling bits for these cells: plane q = 2 * column + row half
-                    // of the tile's 8x8 quarters, two bits (upper / lower 8x4 cell) per entry, and
-                    // the entry's irregular flag
-                    unsigned irr = 0u;
 #pragma unroll
-                    for (int h = 0; h < kCells / 2; ++h) {
-                        const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * (kCells / 2) + h;
-                        const unsigned byte = (unsigned)__ldg(cell_masks + q * mask_stride + my_i);
-                        m |= (byte & 3u) << (2 * h);
-                        irr |= byte & kMaskByteIrregular;
-                    }
-                    if (irr) m |= kCellMaskIrregular;
-                } else {
-                    m = gs_entry_mask<kCells>(n0, n1, n2, x_first, y_first);
-                }
-                if (live & m) my_mask = (live & m) | (m & kCellMaskIrregular);
+                for (int h = 0; h < kCells / 2; ++h)
+                    m |= ((unsigned)__ldg(cell_masks + (q0 + h) * mask_stride + my_i) & 3u) << (2 * h);
+                my_mask = live & m;
             }
         }
-        s_rec[3 * lane] = n0;
-        s_rec[3 * lane + 1] = n1;
-        // the record's pad word carries the entry's decision band to the visits
-        s_rec[3 * lane + 2] = make_float4(n2.x, n2.y, n2.z, decision_band(n0.z, n0.w, n1.x));
+        {
+            const BandConsts band = band_consts(n1.y * n1.z, n2.w);
+            s_rec[3 * lane] = n0;
+            s_rec[3 * lane + 1] = make_float4(n1.x, band.xlo, n1.z, n1.w);  // c xlo opacity red
+            s_rec[3 * lane + 2] = make_float4(n2.x, n2.y, band.hi, n2.w);   // green blue hi s
+        }
         s_out[kGradSlots * lane + 10] = 0.f;
         // ---- prefetch the next batch -----------------------------------------------------------
         {
@@ -253,16 +299,10 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             const unsigned m = __shfl_sync(0xffffffffu, my_mask, k);
             const int i = top - 1 - k;
             const float4 r0 = s_rec[3 * k];      // u v a b
-            const float4 r1 = s_rec[3 * k + 1];  // c rescale alpha red
-            const float4 r2 = s_rec[3 * k + 2];  // green blue z band
+            const float4 r1 = s_rec[3 * k + 1];  // c xlo opacity red
+            const float4 r2 = s_rec[3 * k + 2];  // green blue hi s   (see band_consts)
             const float dx = fx - r0.x;
             const float adx = r0.z * dx, bdx = r0.w * dx;
-            const float peak = r1.y * r1.z;
-            // fast alpha decides outside [lo, hi); inside, and for irregular entries (hi = NaN: no
-            // alpha is ever "safely above"), the literal arithmetic does
-            const bool irregular = (m & kCellMaskIrregular) != 0u;  // warp-uniform
-            const float lo = irregular ? -__int_as_float(0x7f800000) : fmaf(-r2.w, 1.0f / 255.0f, 1.0f / 255.0f);
-            const float hi = irregular ? __int_as_float(0x7fc00000) : fmaf(r2.w, 1.0f / 255.0f, 1.0f / 255.0f);
             float v[10];
 #pragma unroll
             for (int q = 0; q < 10; ++q) v[q] = 0.f;
@@ -271,17 +311,14 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             for (int j = 0; j < kCells; ++j) {
                 if (!((m >> j) & 1u)) continue;  // warp-uniform
                 const float dy = (fy0 + (float)(kCellH * j)) - r0.y;
-                const float v0 = fmaf(r0.w, dy, adx);
-                const float v1 = fmaf(r1.x, dy, bdx);
-                const float quad = fmaf(dy, v1, dx * v0);
-                float prod = fast_ex2(-0.72134752044448170368f * quad) * peak;  // alpha
-                bool take = prod >= lo;
-                if (!(prod >= hi) && (take || irregular)) {  // rare: on the edge, or an irregular entry
-                    const float lit = literal_alpha(dx, dy, r0.z, r0.w, r1.x, r1.y, r1.z);
-                    take = lit >= 1.0f / 255.0f;
-                    if (irregular) prod = lit;  // +inf / NaN handling of the literal exp
-                }
-                if ((i < last[j]) && take) {
+                float v0, v1, xp;
+                const float prod = fast_alpha(dx, dy, adx, bdx, r0.w, r1.x, r2.w, r2.z, v0, v1, xp);
+                if ((i < last[j]) && (xp >= r1.y)) {
+                    // Taken, but below the band's upper edge (x' < 0): the pixel is AMBIGUOUS.  The one
+                    // instruction the hot block spends on it moves the sign bit of x' into last[j]; a
+                    // negative last[j] also ends the pixel's traversal here (i < last[j] fails from now
+                    // on), which the literal pass's replay of this kernel mirrors.
+                    last[j] |= (int)(__float_as_uint(xp) & 0x80000000u);
                     hits += 1;
                     const float a = fminf(prod, 0.99f);
                     const float inv = fast_rcp(1.0f - a);
@@ -333,12 +370,11 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         }
         __syncwarp();
     }
-    if (kMagnitude) {
 #pragma unroll
-        for (int j = 0; j < kCells; ++j) {
-            const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
-            reinterpret_cast<float2 *>(map_on_image)[px] = make_float2(tot0[j], tot1[j]);
-        }
+    for (int j = 0; j < kCells; ++j) {
+        const size_t px = (size_t)(pv0 + kCellH * j) * width + pu;
+        if (last[j] < 0) fix_list[1u + atomicAdd(fix_list, 1u)] = (unsigned)px;  // the literal pass re-does it
+        if (kMagnitude) reinterpret_cast<float2 *>(map_on_image)[px] = make_float2(tot0[j], tot1[j]);
     }
     if (!work) return;
     __syncwarp();  // the next unit restages s_rec / s_out
@@ -346,44 +382,236 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
     gs_retire_warp(work, gridDim.x * kParts);
 }
 
+// ---- the literal pass over flagged pixels ---------------------------------------------------------
+// One pixel, one traversal of its list from last-1 down to the tile start by the whole warp, 32 entries
+// per step (the next step's records are fetched while this one is worked on): every lane forms its
+// pair's alpha and decision independently (neither depends on T), then T = T_end / prod(1 - alpha) and
+// w = sum(alpha T cg) over the entries behind follow from warp scans.  Two variants side by side on the
+// same loads: the reference's arithmetic and decision (contributions ADDED) and, for a pixel the hot
+// kernel did process, the hot kernel's arithmetic and (biased) decision (contributions SUBTRACTED).
+struct FixVariant {
+    bool take;
+    float prod, v0, v1, inv, a;
+    float T_carry, w_carry;
+    float Tn, w_before, term;
+};
+
+__device__ __forceinline__ void fix_scan(FixVariant &x, const float cg, const int lane)
+{
+    // T after this entry = T_carry * (product of inv over lanes 0..l): inclusive scan
+    float scan = x.inv;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float o = __shfl_up_sync(0xffffffffu, scan, d);
+        if (lane >= d) scan *= o;
+    }
+    x.Tn = x.T_carry * scan;
+    // w before this entry = w_carry + sum of (alpha T cg) over lanes 0..l-1: exclusive scan
+    x.term = x.take ? x.a * x.Tn * cg : 0.0f;
+    float wsum = x.term;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const float o = __shfl_up_sync(0xffffffffu, wsum, d);
+        if (lane >= d) wsum += o;
+    }
+    x.w_before = x.w_carry + (wsum - x.term);
+    x.T_carry = __shfl_sync(0xffffffffu, x.Tn, 31);
+    x.w_carry = __shfl_sync(0xffffffffu, x.w_before + x.term, 31);
+}
+
+// the 11 per-pair terms (R.py:645-696) of one variant, times `sign`, into out[]
+template <bool kMagnitude>
+__device__ __forceinline__ void fix_terms(const FixVariant &x, const float sign, const float cg,
+                                          const float opacity, const float g0, const float g1, const float g2,
+                                          float (&out)[11], float &gm0, float &gm1)
+{
+    gm0 = gm1 = 0.f;
+    if (!x.take) return;
+    const float dcol = x.a * x.Tn;
+    const float sa = (x.Tn * cg - x.inv * x.w_before) * x.prod;
+    gm0 = sa * x.v0;
+    gm1 = sa * x.v1;
+    out[0] += sign * gm0;
+    out[1] += sign * gm1;
+    out[2] += sign * 0.5f * gm0 * x.v0;
+    out[3] += sign * 0.5f * gm0 * x.v1;
+    out[4] += sign * 0.5f * gm1 * x.v1;
+    out[5] += sign * dcol * g0;
+    out[6] += sign * dcol * g1;
+    out[7] += sign * dcol * g2;
+    out[8] += sign * sa * (1.0f - opacity);
+    if (kMagnitude) out[9] += sign * sqrtf(fmaf(gm0, gm0, gm1 * gm1));
+    out[10] += sign;
+}
+
+template <bool kMagnitude>
+__device__ __forceinline__ void fixup_pixel(const int lane, const bool replay, const int start, const int last,
+                                            const float fx, const float fy, const float T_end,
+                                            const float g0, const float g1, const float g2,
+                                            const int32_t *__restrict__ payload,
+                                            const float4 *__restrict__ records,
+                                            float *__restrict__ splat_grads, float &tot0, float &tot1)
+{
+    FixVariant lit, fast;
+    bool stopped = false;  // warp-uniform: the replay has passed the hot kernel's last pair of this pixel
+    lit.T_carry = fast.T_carry = T_end;
+    lit.w_carry = fast.w_carry = 0.0f;
+    int g_next = 0;
+    float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
+    {
+        const int i = last - 1 - lane;
+        if (i >= start) {
+            g_next = __ldg(payload + i);
+            const float4 *src = records + (size_t)3 * g_next;
+            n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
+        }
+    }
+    for (int top = last; top > start; top -= kBatch) {
+        const int i = top - 1 - lane;
+        const int g = g_next;
+        const float4 r0 = n0, r1 = n1, r2 = n2;
+        {
+            const int in = i - kBatch;
+            if (in >= start) {
+                g_next = __ldg(payload + in);
+                const float4 *src = records + (size_t)3 * g_next;
+                n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
+            }
+        }
+        const bool valid = i >= start;
+        const float dx = fx - r0.x, dy = fy - r0.y;
+        const float opacity = r1.z;
+        const float cg = fmaf(r2.y, g2, fmaf(r2.x, g1, r1.w * g0));
+        // the reference: utils.py:331-345 in literal fp32, decision R.py:634 (false for NaN)
+        lit.prod = literal_alpha(dx, dy, r0.z, r0.w, r1.x, r1.y, r1.z);
+        lit.v0 = fmaf(r0.w, dy, r0.z * dx);
+        lit.v1 = fmaf(r1.x, dy, r0.w * dx);
+        lit.take = valid && (lit.prod >= kAlphaMin);
+        lit.a = lit.take ? fminf(lit.prod, 0.99f) : 0.0f;
+        lit.inv = lit.take ? 1.0f / (1.0f - lit.a) : 1.0f;
+        fix_scan(lit, cg, lane);
+        float out[11];
+#pragma unroll
+        for (int q = 0; q < 11; ++q) out[q] = 0.f;
+        float gm0, gm1;
+        fix_terms<kMagnitude>(lit, 1.0f, cg, opacity, g0, g1, g2, out, gm0, gm1);
+        if (kMagnitude) {
+            tot0 += fabsf(gm0);
+            tot1 += fabsf(gm1);
+        }
+        if (replay) {  // warp-uniform: what the hot kernel added for this pixel, with the opposite sign
+            const BandConsts band = band_consts(r1.y * r1.z, r2.w);
+            float xp;
+            fast.prod = fast_alpha(dx, dy, r0.z * dx, r0.w * dx, r0.w, r1.x, r2.w, band.hi, fast.v0, fast.v1, xp);
+            fast.take = valid && !stopped && (xp >= band.xlo);
+            // the hot kernel took the first ambiguous pair (x' < 0) of the pixel and nothing after it
+            const unsigned amb = __ballot_sync(0xffffffffu, fast.take && xp < 0.0f);
+            if (amb) {
+                const int first = __ffs(amb) - 1;  // lanes are in traversal order
+                fast.take = fast.take && lane <= first;
+                stopped = true;
+            }
+            fast.a = fast.take ? fminf(fast.prod, 0.99f) : 0.0f;
+            fast.inv = fast.take ? fast_rcp(1.0f - fast.a) : 1.0f;
+            fix_scan(fast, cg, lane);
+            fix_terms<kMagnitude>(fast, -1.0f, cg, opacity, g0, g1, g2, out, gm0, gm1);
+        }
+        if (lit.take || (replay && fast.take)) {
+            float *dst = splat_grads + (size_t)kGradSlots * g;
+#pragma unroll
+            for (int q = 0; q < 11; ++q)
+                if ((kMagnitude || q != 9) && out[q] != 0.0f) atomicAdd(dst + q, out[q]);
+        }
+    }
+}
+
+template <bool kMagnitude>
+__global__ void __launch_bounds__(128)
+blend_bwd_fixup_kernel(int height, int width, const int32_t *__restrict__ tile_start,
+                       const int32_t *__restrict__ tile_end, const int32_t *__restrict__ payload,
+                       const float4 *__restrict__ records, const float *__restrict__ image_grad,
+                       const float *__restrict__ acc_alpha, const int32_t *__restrict__ last_effective,
+                       float *__restrict__ splat_grads, float *__restrict__ map_on_image,
+                       const unsigned *__restrict__ fix_list)
+{
+    const int lane = threadIdx.x & 31;
+    const unsigned count = fix_list[0];
+    const unsigned warps = gridDim.x * (blockDim.x >> 5);
+    const int tiles_per_row = width / kTile;
+    // the flagged pixels are dealt out one per warp, round robin (the list is in no particular order)
+    for (unsigned idx = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); idx < count; idx += warps) {
+        const unsigned entry = fix_list[1u + idx];
+        const bool whole = (entry & kFixWholeBit) != 0u;
+        const long long px = (long long)(entry & ~kFixWholeBit);
+        const int pv = (int)(px / width), pu = (int)(px % width);
+        const int tile = (pv / kTile) * tiles_per_row + pu / kTile;
+        const int start = tile_start[tile], end = tile_end[tile];
+        const int last = (end > start) ? min(last_effective[px], end) : start;
+        const float T_end = 1.0f - acc_alpha[px];
+        const float g0 = image_grad[3 * px], g1 = image_grad[3 * px + 1], g2 = image_grad[3 * px + 2];
+        float tot0 = 0.f, tot1 = 0.f;
+        fixup_pixel<kMagnitude>(lane, !whole, start, last, (float)pu + 0.5f, (float)pv + 0.5f, T_end, g0, g1, g2,
+                                payload, records, splat_grads, tot0, tot1);
+        if (kMagnitude) {
+#pragma unroll
+            for (int d = 16; d > 0; d >>= 1) {
+                tot0 += __shfl_xor_sync(0xffffffffu, tot0, d);
+                tot1 += __shfl_xor_sync(0xffffffffu, tot1, d);
+            }
+            if (lane == 0) reinterpret_cast<float2 *>(map_on_image)[px] = make_float2(tot0, tot1);
+        }
+    }
+}
+
+struct BwdLaunchInfo {
+    int resident = 0;  // CTAs of the hot kernel resident at once on this device
+    int sms = 0;
+};
+
 template <int kCells>
 int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t *tile_start,
                const int32_t *tile_end, const int32_t *payload, const float4 *rec,
                const float *image_grad, const float *acc_alpha, const int32_t *last_effective,
-               float *splat_grads, float *map_on_image, const uint8_t *cell_masks, long long mask_stride)
+               float *splat_grads, float *map_on_image, const uint8_t *cell_masks, long long mask_stride,
+               const uint8_t *quarter_flags, unsigned *fix_list)
 {
     constexpr int kParts = kTilePixels / (kCells * 32);
     constexpr int kThreads = 32 * kParts;
     // persistent launch: as many CTAs as are resident at once, warps pull (tile, part) units
-    static int resident[4] = {0, 0, 0, 0};
-    int &res = resident[(map_on_image ? 2 : 0) + (cell_masks ? 1 : 0)];
-    if (res == 0) {
-        int dev = 0, sms = 0, per_sm = 0;
-        GS_CUDA_TRY(cudaGetDevice(&dev));
-        GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-#define GS_BWD_OCC(MAG, MSK) \
-    GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, MAG, MSK>, kThreads, 0))
-        if (map_on_image) {
-            if (cell_masks) GS_BWD_OCC(true, true); else GS_BWD_OCC(true, false);
-        } else {
-            if (cell_masks) GS_BWD_OCC(false, true); else GS_BWD_OCC(false, false);
-        }
-#undef GS_BWD_OCC
-        res = sms * (per_sm > 0 ? per_sm : 1);
+    static BwdLaunchInfo info[64][2];
+    int dev = 0;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    BwdLaunchInfo &li = info[dev & 63][map_on_image ? 1 : 0];
+    if (li.resident == 0) {
+        int per_sm = 0;
+        GS_CUDA_TRY(cudaDeviceGetAttribute(&li.sms, cudaDevAttrMultiProcessorCount, dev));
+        if (map_on_image)
+            GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, true>, kThreads, 0));
+        else
+            GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, false>, kThreads, 0));
+        li.resident = li.sms * (per_sm > 0 ? per_sm : 1);
     }
+    GS_CUDA_TRY(cudaMemsetAsync(fix_list, 0, sizeof(unsigned), st));  // the list's counter
     const char *pe = getenv("GS_BLEND_PERSISTENT");  // 0: one CTA per tile (A/B and tests; read per call)
     GsWorkCounter *work = (pe && atoi(pe) == 0) ? nullptr : gs_work_counter(st);
     const unsigned units = (unsigned)tiles * kParts;
-    const int grid = work ? (tiles < res ? tiles : res) : tiles;
-#define GS_BWD_LAUNCH(MAG, MSK)                                                                        \
-    blend_bwd_kernel<kCells, MAG, MSK><<<grid, kThreads, 0, st>>>(                                      \
-        height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,      \
-        splat_grads, map_on_image, cell_masks, mask_stride, work, units)
-    if (map_on_image) {
-        if (cell_masks) GS_BWD_LAUNCH(true, true); else GS_BWD_LAUNCH(true, false);
-    } else {
-        if (cell_masks) GS_BWD_LAUNCH(false, true); else GS_BWD_LAUNCH(false, false);
-    }
+    const int grid = work ? (tiles < li.resident ? tiles : li.resident) : tiles;
+    // the literal pass: a fixed grid (the list's length is known on the device only), one flagged pixel
+    // per warp and round; with an empty list -- the common case away from thresholds -- it costs a launch
+    const long long fix_ctas = 4ll * li.sms;
+    const char *fe = getenv("GS_BWD_FIXUP");  // 0: timing experiments only (results are then NOT exact)
+    const bool fixup = !(fe && atoi(fe) == 0);
+#define GS_BWD_LAUNCH(MAG)                                                                              \
+    do {                                                                                                \
+        blend_bwd_kernel<kCells, MAG><<<grid, kThreads, 0, st>>>(                                       \
+            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,   \
+            splat_grads, map_on_image, cell_masks, mask_stride, quarter_flags, fix_list, work, units);  \
+        GS_LAUNCH_CHECK();                                                                              \
+        if (fixup) blend_bwd_fixup_kernel<MAG><<<(unsigned)fix_ctas, 128, 0, st>>>(                     \
+            height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,   \
+            splat_grads, map_on_image, fix_list);                                                       \
+    } while (0)
+    if (map_on_image) GS_BWD_LAUNCH(true); else GS_BWD_LAUNCH(false);
 #undef GS_BWD_LAUNCH
     GS_LAUNCH_CHECK();
     return GS_OK;
@@ -391,16 +619,26 @@ int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t 
 
 }  // namespace
 
+extern "C" int64_t gs_blend_bwd_scratch_bytes(int height, int width)
+{
+    // {count, one entry per pixel at most}: every pixel is appended at most once per call
+    return (height > 0 && width > 0) ? 4 * ((int64_t)height * width + 1) : 0;
+}
+
 extern "C" int gs_blend_bwd(int height, int width, const int32_t *tile_start,
                             const int32_t *tile_end, const int32_t *sorted_payload,
                             const float *records, const float *image_grad, const float *acc_alpha,
                             const int32_t *last_effective, float *splat_grads, float *map_on_image,
-                            const uint8_t *cell_masks, int64_t mask_stride, void *stream)
+                            const uint8_t *cell_masks, int64_t mask_stride, const uint8_t *quarter_flags,
+                            void *scratch, void *stream)
 {
-    if (cell_masks && mask_stride < 0) return GS_E_INVALID;
+    if (mask_stride < 0) return GS_E_INVALID;
     if (height <= 0 || width <= 0 || height % kTile || width % kTile) return GS_E_INVALID;
     if (!tile_start || !tile_end || !image_grad || !acc_alpha || !last_effective || !splat_grads)
         return GS_E_INVALID;
+    // the culling bits and the irregular flags of the forward blend of the SAME lists are required: the
+    // backward never redoes the culling arithmetic
+    if (!cell_masks || !quarter_flags || !scratch) return GS_E_INVALID;
     int tiles = (width / kTile) * (height / kTile);
     static int cells = 0;
     if (cells == 0) {
@@ -413,8 +651,8 @@ extern "C" int gs_blend_bwd(int height, int width, const int32_t *tile_start,
     if (cells == 2)
         return launch_bwd<2>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
                              image_grad, acc_alpha, last_effective, splat_grads, map_on_image, cell_masks,
-                             mask_stride);
+                             mask_stride, quarter_flags, (unsigned *)scratch);
     return launch_bwd<4>(tiles, st, height, width, tile_start, tile_end, sorted_payload, rec,
                          image_grad, acc_alpha, last_effective, splat_grads, map_on_image, cell_masks,
-                         mask_stride);
+                         mask_stride, quarter_flags, (unsigned *)scratch);
 }

@@ -189,7 +189,8 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                  const float4 *__restrict__ records, float *__restrict__ image,
                  float *__restrict__ depth, float *__restrict__ acc_alpha,
                  int32_t *__restrict__ last_effective, int32_t *__restrict__ valid_count,
-                 uint8_t *__restrict__ cell_masks, const long long mask_stride)
+                 uint8_t *__restrict__ cell_masks, const long long mask_stride,
+                 uint8_t *__restrict__ quarter_flags)
 {
     constexpr int kParts = kTilePixels / (kPairs * 64);  // warps per tile
     constexpr int kPartsPerColumn = kParts / 2;
@@ -222,6 +223,7 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
     }
     st.live = (1u << (2 * kPairs)) - 1u;
     unsigned open = kAllPairs;  // pair cells that still have an unsaturated pixel (warp-uniform)
+    unsigned seen_irregular = 0u;  // some entry this warp had to look at is irregular (warp-uniform)
 
     // software pipeline: records of the next batch in registers, payload two batches ahead
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
@@ -250,8 +252,7 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
 #pragma unroll
                 for (int c = 0; c < kPairs; ++c) {
                     const int q = 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * kPairs + c;
-                    cell_masks[q * mask_stride + base + lane] =
-                        (uint8_t)(((fine >> (2 * c)) & 3u) | ((fine & kCellMaskIrregular) ? kMaskByteIrregular : 0u));
+                    cell_masks[q * mask_stride + base + lane] = (uint8_t)((fine >> (2 * c)) & 3u);
                 }
             }
             my_mask = (raw & open) ? (raw & (open | kCellMaskIrregular)) : 0u;
@@ -272,6 +273,7 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
 
         unsigned pending = __ballot_sync(0xffffffffu, my_mask != 0u);
         const unsigned irregular = __ballot_sync(0xffffffffu, (my_mask & kCellMaskIrregular) != 0u);
+        seen_irregular |= irregular;
         while (pending) {
             const int k = __ffs(pending) - 1;
             pending &= pending - 1u;
@@ -308,6 +310,14 @@ blend_fwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         __syncwarp();
     }
 
+    // tells the backward blend that this 8x8 quarter's list holds an irregular entry among those its
+    // pixels reach: the backward then leaves the quarter to its literal (guarded) pass
+    if (quarter_flags && lane == 0) {
+#pragma unroll
+        for (int c = 0; c < kPairs; ++c)
+            quarter_flags[4 * tile + 2 * (part / kPartsPerColumn) + (part % kPartsPerColumn) * kPairs + c] =
+                seen_irregular ? 1 : 0;
+    }
 #pragma unroll
     for (int c = 0; c < kPairs; ++c) {
         float T[2];
@@ -332,17 +342,18 @@ template <int kPairs>
 int launch_fwd(int tiles, cudaStream_t st, int rgb_only, int height, int width,
                const int32_t *tile_start, const int32_t *tile_end, const int32_t *payload,
                const float4 *rec, float *image, float *depth, float *acc_alpha,
-               int32_t *last_effective, int32_t *valid_count, uint8_t *cell_masks, long long mask_stride)
+               int32_t *last_effective, int32_t *valid_count, uint8_t *cell_masks, long long mask_stride,
+               uint8_t *quarter_flags)
 {
     constexpr int kThreads = 32 * (kTilePixels / (kPairs * 64));
     if (rgb_only)
         blend_fwd_kernel<kPairs, true><<<tiles, kThreads, 0, st>>>(
             height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
-            last_effective, valid_count, cell_masks, mask_stride);
+            last_effective, valid_count, cell_masks, mask_stride, quarter_flags);
     else
         blend_fwd_kernel<kPairs, false><<<tiles, kThreads, 0, st>>>(
             height, width, tile_start, tile_end, payload, rec, image, depth, acc_alpha,
-            last_effective, valid_count, cell_masks, mask_stride);
+            last_effective, valid_count, cell_masks, mask_stride, quarter_flags);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
@@ -353,9 +364,10 @@ extern "C" int gs_blend_fwd(int height, int width, const int32_t *tile_start,
                             const int32_t *tile_end, const int32_t *sorted_payload,
                             const float *records, float *image, float *depth, float *acc_alpha,
                             int32_t *last_effective, int32_t *valid_count, int rgb_only,
-                            uint8_t *cell_masks, int64_t mask_stride, void *stream)
+                            uint8_t *cell_masks, int64_t mask_stride, uint8_t *quarter_flags, void *stream)
 {
     if (cell_masks && mask_stride < 0) return GS_E_INVALID;
+    if ((cell_masks == nullptr) != (quarter_flags == nullptr)) return GS_E_INVALID;  // both or neither
     if (height <= 0 || width <= 0 || height % kTile || width % kTile) return GS_E_INVALID;
     if (!tile_start || !tile_end || !image) return GS_E_INVALID;
     if (!rgb_only && (!depth || !acc_alpha || !last_effective || !valid_count)) return GS_E_INVALID;
@@ -370,7 +382,9 @@ extern "C" int gs_blend_fwd(int height, int width, const int32_t *tile_start,
     cudaStream_t st = (cudaStream_t)stream;
     if (pairs == 1)
         return launch_fwd<1>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload, rec,
-                             image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride);
+                             image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride,
+                             quarter_flags);
     return launch_fwd<2>(tiles, st, rgb_only, height, width, tile_start, tile_end, sorted_payload, rec,
-                         image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride);
+                         image, depth, acc_alpha, last_effective, valid_count, cell_masks, mask_stride,
+                         quarter_flags);
 }

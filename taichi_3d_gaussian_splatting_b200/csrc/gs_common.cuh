@@ -111,6 +111,29 @@ __device__ __forceinline__ void gs_sh_basis(float dx, float dy, float dz, float 
     b[15] = (float)0.59004358992664352 * x * (-x * x + 3.0f * y * y);
 }
 
+// ---- decision band of the backward blend ------------------------------------------------------------
+// The backward blend forms alpha with fast arithmetic (FMA-contracted quadratic form, ex2.approx) but
+// must take the reference's decision alpha >= 1/255, which the reference takes on ITS fp32 arithmetic
+// (R.py:634, utils.py:331-345).  band = a bound of the relative difference between the two alphas of a
+// pair of this splat NEAR the threshold: the quadratic forms differ by <= 7 u P (u = 2^-24, P = sum of
+// the magnitudes of the form's terms <= quad (1 + rho) / (1 - rho), rho = |b| / sqrt(a c), and
+// quad = tau = 2 ln(255 peak) at the threshold), i.e. 2.1e-7 tau (1 + rho) / (1 - rho) in alpha; the
+// exponentials, the constants and the products add 1.5e-6.  Both with a factor >= 2 of slack; capped at
+// 2 % (the forward's culling bits guarantee alpha < 0.9754 / 255 for the pairs they drop, so a dropped
+// pair is never one the band could reach; the cap is met beyond an axis ratio of ~50 : 1 at full
+// opacity, where the bound stops being rigorous).
+// Returned, and stored as the 12th float of the splat's record: s = log2(peak / hi) with
+// hi = (1 + band) / 255 -- the form the backward's inner loop consumes (blend_bwd.cu, band_consts).
+__device__ __forceinline__ float gs_decision_band_log2(float a, float b, float c, float peak)
+{
+    if (!(peak > 0.0f) || !(a > 0.0f) || !(c > 0.0f) || !(a * c > b * b) || !isfinite(a + b + c + peak))
+        return 0.0f;  // never reaches the threshold, or irregular (decided by the literal pass alone)
+    const float rho = fminf(sqrtf((b * b) / (a * c)), 0.9999f);
+    const float tau = fmaxf(2.0f * logf(255.0f * peak), 0.0f);
+    const float band = fminf(3e-6f + 6e-7f * tau * ((1.0f + rho) / (1.0f - rho)), 0.02f);
+    return log2f((255.0f * peak) / (1.0f + band));
+}
+
 // ---- per-cell culling shared by the two blend kernels --------------------------------------------
 // A warp owns a column of kCells cells of 8x4 pixels.  Bit j of the result is set <=> the splat
 // may reach alpha >= 1/255 at a pixel centre of cell j (rows [kRows j, kRows (j+1)) of the column, first
@@ -152,8 +175,10 @@ __device__ __forceinline__ unsigned gs_cell_mask(float u, float v, float a, floa
 // r2 = green blue depth pad) for a warp's kCells cells, as BOTH blend kernels must see them: entries
 // with a conic that is not positive definite / finite, or with a non-finite colour / depth / opacity,
 // keep every bit and carry kCellMaskIrregular -- they take the guarded literal arithmetic in the forward
-// (the masked "add zero" of the packed path is not a no-op for them) and in the backward (the decision
-// alpha >= 1/255 is then taken with the literal exp, never with ex2.approx of a positive / NaN exponent).
+// (the masked "add zero" of the packed path is not a no-op for them); the forward also flags the 8x8
+// quarters whose pixels reach such an entry, and the backward leaves those quarters to its literal pass
+// (the decision alpha >= 1/255 is then taken with the literal exp, never with ex2.approx of a positive
+// / NaN exponent).
 template <int kCells>
 __device__ __forceinline__ unsigned gs_entry_mask(const float4 &r0, const float4 &r1, const float4 &r2,
                                                   float x_first, float y_first)
@@ -163,9 +188,6 @@ __device__ __forceinline__ unsigned gs_entry_mask(const float4 &r0, const float4
         fine = ((1u << kCells) - 1u) | kCellMaskIrregular;
     return fine;
 }
-// bit of a cell_masks byte (two culling bits per 8x8 quarter in bits 0-1) that carries kCellMaskIrregular
-constexpr unsigned kMaskByteIrregular = 4u;
-
 __device__ __forceinline__ unsigned long long gs_ld_volatile_u64(const unsigned long long *p)
 {
     return *reinterpret_cast<const volatile unsigned long long *>(p);

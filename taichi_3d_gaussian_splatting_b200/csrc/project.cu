@@ -15,6 +15,13 @@ constexpr int kProjBlock = 256;
 constexpr unsigned long long kFlagAggregate = 1ull << 62;
 constexpr unsigned long long kFlagPrefix = 2ull << 62;
 constexpr unsigned long long kValueMask = (1ull << 62) - 1;
+// Look-back word.  Default: the number of visible points alone (n < 2^30 cannot overflow 62 bits; the
+// total tile count K is summed separately, 64-bit, with one atomic per block).  With per-point tile
+// OFFSETS requested (the literal key pipeline), the word packs (visible << 35 | tiles): 27 bits of
+// points and 35 bits of tiles, and the entry point refuses inputs whose worst case n * tiles-per-image
+// does not fit (GS_E_CAPACITY) instead of letting the tile sum carry into the point count.
+constexpr int kPackShift = 35;
+constexpr unsigned long long kPackTileMask = (1ull << kPackShift) - 1;
 
 __global__ void inverse_pose_kernel(const float *__restrict__ q_pc_cam,
                                     const float *__restrict__ t_pc_cam, int n_obj,
@@ -121,14 +128,17 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
         : "memory");
 }
 
-// kBulk: feature rows come through shared memory by cp.async.bulk (needs a 16-byte aligned
-// features pointer); otherwise every thread reads its own row from global memory.
-template <bool kBulk>
+// Feature rows come through shared memory by cp.async.bulk (the features pointer must be 16-byte
+// aligned; the entry point checks).  kOffsets: also produce the exclusive scan of the tile counts
+// (tile_offsets), which only the literal key pipeline reads.
+template <bool kOffsets>
 __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectParams p)
 {
+    constexpr bool kBulk = true;
     extern __shared__ __align__(128) unsigned char s_dyn[];
     __shared__ unsigned int s_ticket;
     __shared__ unsigned long long s_warp_total[kProjBlock / 32];
+    __shared__ unsigned long long s_warp_tiles[kProjBlock / 32];
     __shared__ unsigned long long s_block_excl;
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -260,24 +270,40 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
 
 
     // ---- ordered compaction, part 1: block scan, publish the block aggregate ----------------
-    unsigned long long mine = ((unsigned long long)(visible ? 1u : 0u) << 32) | (unsigned int)count;
-    unsigned long long incl = mine;
+    unsigned long long mine, incl;
+    if (kOffsets) {
+        mine = ((unsigned long long)(visible ? 1u : 0u) << kPackShift) | (unsigned int)count;
+        incl = mine;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) {
-        unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
-        if (lane >= d) incl += o;
+        for (int d = 1; d < 32; d <<= 1) {
+            unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += o;
+        }
+        if (lane == 31) s_warp_total[warp] = incl;
+    } else {
+        // rank among the warp's visible points by ballot; the tiles are only summed
+        const unsigned ballot = __ballot_sync(0xffffffffu, visible);
+        mine = visible ? 1ull : 0ull;
+        incl = (unsigned long long)__popc(ballot & (0xffffffffu >> (31 - lane)));
+        const unsigned tiles = __reduce_add_sync(0xffffffffu, (unsigned)count);
+        if (lane == 31) {
+            s_warp_total[warp] = incl;
+            s_warp_tiles[warp] = tiles;
+        }
     }
-    if (lane == 31) s_warp_total[warp] = incl;
     __syncthreads();
-    unsigned long long warp_excl = 0, block_total = 0;
+    unsigned long long warp_excl = 0, block_total = 0, block_tiles = 0;
 #pragma unroll
     for (int w = 0; w < kProjBlock / 32; ++w) {
         unsigned long long t = s_warp_total[w];
         if (w < warp) warp_excl += t;
         block_total += t;
+        if (!kOffsets) block_tiles += s_warp_tiles[w];
     }
-    if (tid == 0)
+    if (tid == 0) {
         gs_st_volatile_u64(p.status + block, (block == 0 ? kFlagPrefix : kFlagAggregate) | block_total);
+        if (!kOffsets && block_tiles) atomicAdd(reinterpret_cast<unsigned long long *>(p.totals) + 1, block_tiles);
+    }
 
     // Phase 2: the rest of the per-point attributes (R.py:286-310)
     if (visible) {
@@ -341,8 +367,12 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
             s_block_excl = excl;
             if (block == p.num_blocks - 1) {
                 unsigned long long tot = excl + block_total;
-                p.totals[0] = (long long)(tot >> 32);
-                p.totals[1] = (long long)(tot & 0xffffffffull);
+                if (kOffsets) {
+                    p.totals[0] = (long long)(tot >> kPackShift);
+                    p.totals[1] = (long long)(tot & kPackTileMask);
+                } else {
+                    p.totals[0] = (long long)tot;  // totals[1] = K: summed by the blocks' atomics
+                }
             }
         }
     }
@@ -350,23 +380,25 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     if (!visible) return;
 
     unsigned long long my_excl = s_block_excl + warp_excl + (incl - mine);
-    const long long idx = (long long)(my_excl >> 32);
-    const long long koff = (long long)(my_excl & 0xffffffffull);
+    const long long idx = kOffsets ? (long long)(my_excl >> kPackShift) : (long long)my_excl;
 
+    // what the path itself reads: ids, camera-space position, the packed record, bbox, depth key
     p.ids[idx] = (int32_t)i;
-    reinterpret_cast<float2 *>(p.point_uv)[idx] = make_float2(u, v);
     p.point_in_camera[3 * idx] = cx; p.point_in_camera[3 * idx + 1] = cy;
     p.point_in_camera[3 * idx + 2] = cz;
-    reinterpret_cast<float4 *>(p.conic)[idx] = make_float4(conic0, conic1, conic2, rescale);
-    p.alpha[idx] = alpha;
-    p.color[3 * idx] = col0; p.color[3 * idx + 1] = col1; p.color[3 * idx + 2] = col2;
-    p.radii[idx] = radius;
-    p.num_tiles[idx] = count;
-    p.tile_offsets[idx] = koff;
+    // the reference-named per-point buffers (R.py:873-884), for callers that look at them (the
+    // backward hook's payload: uv and tile counts; tests: all of them)
+    if (p.point_uv) reinterpret_cast<float2 *>(p.point_uv)[idx] = make_float2(u, v);
+    if (p.conic) reinterpret_cast<float4 *>(p.conic)[idx] = make_float4(conic0, conic1, conic2, rescale);
+    if (p.alpha) p.alpha[idx] = alpha;
+    if (p.color) { p.color[3 * idx] = col0; p.color[3 * idx + 1] = col1; p.color[3 * idx + 2] = col2; }
+    if (p.radii) p.radii[idx] = radius;
+    if (p.num_tiles) p.num_tiles[idx] = count;
+    if (kOffsets) p.tile_offsets[idx] = (long long)(my_excl & kPackTileMask);
     float4 *rec = reinterpret_cast<float4 *>(p.records + (size_t)kRecFloats * idx);
     rec[0] = make_float4(u, v, conic0, conic1);
     rec[1] = make_float4(conic2, rescale, alpha, col0);
-    rec[2] = make_float4(col1, col2, cz, 0.0f);
+    rec[2] = make_float4(col1, col2, cz, gs_decision_band_log2(conic0, conic1, conic2, rescale * alpha));
     reinterpret_cast<ushort4 *>(p.bbox)[idx] =
         make_ushort4((unsigned short)tu0, (unsigned short)tu1, (unsigned short)tv0, (unsigned short)tv1);
     p.depth_key[idx] = (int32_t)(cz * p.key_scale);
@@ -405,14 +437,20 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
     if (n >= (1ll << 30)) return GS_E_CAPACITY;
     if (!totals || !workspace) return GS_E_INVALID;
     cudaStream_t st = (cudaStream_t)stream;
-    if (n == 0) {
-        GS_CUDA_TRY(cudaMemsetAsync(totals, 0, 16, st));
-        return GS_OK;
-    }
+    GS_CUDA_TRY(cudaMemsetAsync(totals, 0, 16, st));
+    if (n == 0) return GS_OK;
     if (!xyz || !features || !invalid_mask || !object_id || !intrinsics || !q_cam_pc || !t_cam_pc ||
-        !ids || !point_uv || !point_in_camera || !conic || !alpha || !color || !radii ||
-        !num_tiles || !tile_offsets || !records || !bbox || !depth_key)
+        !ids || !point_in_camera || !records || !bbox || !depth_key)
         return GS_E_INVALID;
+    // the feature rows are fetched with cp.async.bulk and written back as 16-byte vectors
+    if (((uintptr_t)features % 16) != 0 || ((uintptr_t)records % 16) != 0) return GS_E_INVALID;
+    const bool offsets = tile_offsets != nullptr;
+    if (offsets) {
+        // worst case of the packed look-back word: every point covers the whole image
+        const long long tiles_per_image = (long long)(width / kTile) * (height / kTile);
+        if (n >= (1ll << (62 - kPackShift)) || n * tiles_per_image > (long long)kPackTileMask)
+            return GS_E_CAPACITY;
+    }
     ProjectParams p;
     p.xyz = xyz; p.features = features; p.invalid_mask = invalid_mask; p.object_id = object_id;
     p.n = n; p.intrinsics = intrinsics; p.q_cam_pc = q_cam_pc; p.t_cam_pc = t_cam_pc;
@@ -427,17 +465,19 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
     p.status = (unsigned long long *)workspace;
     p.ticket = (unsigned int *)((unsigned long long *)workspace + blocks);
     GS_CUDA_TRY(cudaMemsetAsync(workspace, 0, (size_t)gs_project_workspace_bytes(n), st));
-    if (((uintptr_t)features % 16) == 0) {
-        static bool attr_set = false;
-        if (!attr_set) {
-            GS_CUDA_TRY(cudaFuncSetAttribute(project_cull_sh_kernel<true>,
-                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kProjSmem));
-            attr_set = true;
-        }
-        project_cull_sh_kernel<true><<<blocks, kProjBlock, kProjSmem, st>>>(p);
-    } else {
-        project_cull_sh_kernel<false><<<blocks, kProjBlock, 0, st>>>(p);
+    static GsPerDeviceOnce attr_set;
+    int dev = 0;
+    if (attr_set.need(dev)) {
+        GS_CUDA_TRY(cudaFuncSetAttribute(project_cull_sh_kernel<true>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kProjSmem));
+        GS_CUDA_TRY(cudaFuncSetAttribute(project_cull_sh_kernel<false>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kProjSmem));
+        attr_set.mark(dev);
     }
+    if (offsets)
+        project_cull_sh_kernel<true><<<blocks, kProjBlock, kProjSmem, st>>>(p);
+    else
+        project_cull_sh_kernel<false><<<blocks, kProjBlock, kProjSmem, st>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }

@@ -53,8 +53,21 @@ def test_sort_key_bits():
     assert sort_key_bits(0.0, 10., 100., 1) == (10, 1)
 
 
+def test_point_buffers_hold_only_what_was_asked_for():
+    core = impl._PointBuffers(1000, torch.device("cpu"))
+    assert set(core.offsets) == set(impl._PointBuffers.CORE)
+    assert core.ptr("conic") is None and core.ptr("tile_offsets") is None and core.ptr("records") is not None
+    per_point = sum(cols * torch.empty((), dtype=dtype).element_size()
+                    for name, dtype, cols in core.FIELDS if name in core.offsets)
+    assert per_point == 76   # ids 4 + camera-space xyz 12 + record 48 + bbox 8 + depth key 4
+    hook = impl._PointBuffers(1000, torch.device("cpu"), hook=True)
+    assert set(hook.offsets) == set(impl._PointBuffers.CORE) | {"point_uv", "num_tiles"}
+    literal = impl._PointBuffers(1000, torch.device("cpu"), offsets=True)
+    assert set(literal.offsets) == set(impl._PointBuffers.CORE) | {"tile_offsets"}
+
+
 def test_point_buffers_are_aligned_and_disjoint():
-    buf = impl._PointBuffers(1000, torch.device("cpu"))
+    buf = impl._PointBuffers(1000, torch.device("cpu"), debug=True, offsets=True)
     spans = []
     for name, dtype, cols in buf.FIELDS:
         size = 1000 * cols * torch.empty((), dtype=dtype).element_size()

@@ -465,11 +465,31 @@ def test_training_loop_reduces_loss():
     assert losses[-1] < 0.7 * losses[0], (losses[0], losses[-1])
 
 
-def test_full_size_c2_against_oracle(oracle32, oracle64):
-    """BASELINE.json config 2 at full size: 1M Gaussians, 1920x1088, SH degree 3 -- every forward
-    stage value-exact against the oracle, gradients at 1e-4, plus size-independent properties."""
-    scene = make_scene(1_000_000, 1920, 1088, seed=1002, scale_factor=0.004)
-    got = util.cuda_forward_stages(scene)
+FULL_SIZE_CASES = {
+    # name: (bench workload, (near, far, key scale), tile-row band of the gradient check or None)
+    "c2": ("c2_1m_1920x1088", (0.8, 1000.0, 100.0), None),
+    "c3": ("c3_430k_976x544", (0.8, 1000.0, 100.0), None),
+    # the Truck run's rasteriser values (reference config/tat_truck_every_8_test.yaml:44-47)
+    "c3_truck_cfg": ("c3_430k_976x544", (0.4, 2000.0, 10.0), None),
+    # depth-complexity stress: 186 M list entries, lists of several thousand per tile (a band of tile
+    # rows could be given here to bound the oracle's time: the cotangent is then zero outside it, so the
+    # pairs outside contribute exact zeros; the whole 4K frame takes the oracle ~25 s on 16 cores)
+    "c5": ("c5_5m_3840x2160", (0.8, 1000.0, 100.0), None),
+}
+
+
+@pytest.mark.parametrize("case", list(FULL_SIZE_CASES))
+def test_full_size_against_oracle(oracle32, oracle64, case):
+    """BASELINE.json configs 2, 3 and 5 at FULL size against the oracle: every forward stage value-exact
+    (ids, attributes, tile counts, keys, sorted order, ranges, image, depth, alpha, last index, counts),
+    gradients at 1e-4 against the fp64 arbiter (whole tensor, per column and per row), plus
+    size-independent properties."""
+    import time
+    import bench
+    workload, (near, far, scale), band = FULL_SIZE_CASES[case]
+    n, w, h, sf, seed = bench.WORKLOADS[workload]
+    scene = make_scene(n, w, h, seed=seed, scale_factor=sf)
+    got = util.cuda_forward_stages(scene, near, far, scale)
     keys = got["point_in_camera_sort_key"]
     assert np.all(keys[1:] >= keys[:-1])
     assert int(got["num_overlap_tiles"].sum()) == keys.shape[0]
@@ -478,29 +498,49 @@ def test_full_size_c2_against_oracle(oracle32, oracle64):
     assert np.array_equal(np.bincount(pay, minlength=got["num_overlap_tiles"].shape[0]),
                           got["num_overlap_tiles"])
     assert np.isfinite(got["rasterized_image"]).all()
-    lists = (got["tile_points_end"] - got["tile_points_start"]).reshape(1088 // 16, 1920 // 16)
+    lists = (got["tile_points_end"] - got["tile_points_start"]).reshape(h // 16, w // 16)
     per_pixel_len = np.repeat(np.repeat(lists, 16, 0), 16, 1)
     assert np.all(got["pixel_valid_point_count"] <= per_pixel_len)
-    ref = util.oracle_forward(oracle32, scene)
+    t0 = time.time()
+    ref = util.oracle_forward(oracle32, scene, near, far, scale)
+    t_fwd = time.time() - t0
     report = util.mismatch_report(ref, got)
     assert not report, "\n".join(report)
+    m, k = ref["point_id_in_camera_list"].shape[0], keys.shape[0]
+    del got
 
-    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
-    from taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation import GaussianPointCloudRasterisation
-    g = np.random.default_rng(3).uniform(0, 1, (1088, 1920, 3)).astype(np.float32)
-    ref64 = {k: (v.astype(np.float64) if isinstance(v, np.ndarray) and v.dtype == np.float32 else v)
-             for k, v in ref.items()}
-    b64 = oracle64.backward(ref64, g.astype(np.float64), 3)
+    g = np.random.default_rng(3).uniform(0, 1, (h, w, 3)).astype(np.float32)
+    if band is not None:
+        g[:16 * band[0]] = 0
+        g[16 * band[1]:] = 0
+        oracle64.set_tile_row_band(*band)
+    ref64 = {key: (v.astype(np.float64) if isinstance(v, np.ndarray) and v.dtype == np.float32 else v)
+             for key, v in ref.items()}
+    t0 = time.time()
+    try:
+        b64 = oracle64.backward(ref64, g.astype(np.float64), 3)
+    finally:
+        oracle64.set_tile_row_band(-1, -1)
+    t_bwd = time.time() - t0
+    del ref64
     t = util.scene_tensors(scene, requires_grad=True)
-    ras = _module()
+    hooked = {}
+    ras = _module(near, far, scale, hook=(lambda hk: hooked.update(h=hk)) if band is None else None)
     image, _, _ = _call(ras, scene, t, band=3)
     (image * torch.from_numpy(g).cuda()).sum().backward()
+    print(f"{case}: M={m} K={k} pairs fwd {ref['pairs_fwd']} bwd {b64['pairs_bwd']}; "
+          f"oracle forward {t_fwd:.1f} s, fp64 backward {t_bwd:.1f} s")
     for name, cuda, o64 in (("xyz", t["point_cloud"].grad.cpu().numpy(), b64["grad_pointcloud"]),
                             ("features", t["point_cloud_features"].grad.cpu().numpy(),
                              b64["grad_pointcloud_features"])):
         l2, mx = util.grad_error(o64, cuda)
-        print(f"C2 grad {name}: rel-l2 {l2:.2e} max-col-norm {mx:.2e}")
+        rows = util.row_error_summary(o64, cuda)
+        print(f"{case} grad {name}: rel-l2 {l2:.2e} max-col-norm {mx:.2e} per-row p50 {rows['p50']:.1e} "
+              f"p99 {rows['p99']:.1e} p99.9 {rows['p999']:.1e} max {rows['max']:.1e} ({rows['rows']} rows)")
         assert l2 <= 1e-4 and mx <= 1e-4
+        assert rows["p99"] <= 1e-4
+    if band is None:  # the whole frame went through both: the same pairs took part
+        assert np.array_equal(hooked["h"].num_affected_pixels.cpu().numpy(), b64["num_affected_pixels"])
 
 
 def test_accumulate_gradients_into_sums_views():
@@ -568,34 +608,6 @@ def test_view_sharded_step_on_two_lanes_matches_one_lane():
             assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
 
 
-def test_backward_with_and_without_the_forward_cell_masks():
-    """gs_blend_bwd either reads the culling bits gs_blend_fwd stored (default) or recomputes them;
-    both visit every contributing (pixel, entry) pair, so the gradients agree to rounding."""
-    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
-    scene = make_scene(30000, 256, 160, seed=27, scale_factor=0.015)
-    g = torch.from_numpy(np.random.default_rng(5).uniform(0, 1, (160, 256, 3)).astype(np.float32)).cuda()
-    grads = []
-    saved = impl.REUSE_CELL_MASKS
-    try:
-        for reuse in (True, False):
-            impl.REUSE_CELL_MASKS = reuse
-            hooked = {}
-            ras = _module(hook=lambda h: hooked.update(h=h))
-            t = util.scene_tensors(scene, requires_grad=True)
-            image, _, _ = _call(ras, scene, t, band=3)
-            (image * g).sum().backward()
-            grads.append((t["point_cloud"].grad.cpu().numpy(), t["point_cloud_features"].grad.cpu().numpy(),
-                          hooked["h"].num_affected_pixels.cpu().numpy(),
-                          hooked["h"].magnitude_grad_viewspace_on_image.cpu().numpy()))
-    finally:
-        impl.REUSE_CELL_MASKS = saved
-    assert np.array_equal(grads[0][2], grads[1][2])          # the same pairs were visited
-    for a, b in zip(grads[0][:2], grads[1][:2]):
-        l2, mx = util.grad_error(b, a)
-        assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
-    assert np.allclose(grads[0][3], grads[1][3], rtol=1e-4, atol=1e-7)
-
-
 def test_persistent_blend_launch_equals_one_cta_per_tile(monkeypatch):
     """The backward blend's persistent launch (warps pull (tile, part) units from a per-stream counter
     that the last warp re-arms) against the plain one-CTA-per-tile launch (GS_BLEND_PERSISTENT=0):
@@ -625,7 +637,7 @@ def test_persistent_blend_launch_equals_one_cta_per_tile(monkeypatch):
                 assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
 
 
-@pytest.mark.parametrize("workload", ["c3_430k_976x544", "c4_2m_976x544", "c5_5m_3840x2160"])
+@pytest.mark.parametrize("workload", ["c4_2m_976x544", "c5_5m_3840x2160"])
 def test_full_size_properties_of_the_other_baseline_configs(workload):
     """BASELINE.json configs 3-5 at full size, through size-independent properties (the oracle
     comparison at these sizes is config 2's, above): the sorted keys are sorted and stable, the tile
@@ -670,7 +682,7 @@ def test_full_size_properties_of_the_other_baseline_configs(workload):
 
 
 def _blend_case_by_hand(seed=0):
-    """A 32x32 image (4 tiles) whose every tile lists every splat, with three kinds of entries the
+    """A 32x32 image (4 tiles) whose tiles list (nearly) every splat, with three kinds of entries the
     synthetic scenes never produce: (a) conics that are NOT positive definite (an exponent above zero:
     only the guarded literal path may see it), (b) a NaN opacity (the forward takes such a pair --
     `alpha < 1/255` is false -- the backward skips it -- `alpha >= 1/255` is false: R.py:451 vs :634),
@@ -709,10 +721,15 @@ def _blend_case_by_hand(seed=0):
     color = rng.uniform(0.05, 1.0, (m, 3)).astype(np.float32)
     xyz_cam = np.zeros((m, 3), np.float32)
     xyz_cam[:, 2] = rng.uniform(1, 20, m).astype(np.float32)
-    order = rng.permutation(m).astype(np.int32)           # one list order, shared by the four tiles
-    payload = np.tile(order, 4)
-    start = (np.arange(4) * m).astype(np.int32)
-    end = start + m
+    # tiles 0 and 1 list every splat, tiles 2 and 3 only the regular and edge ones: the backward must take
+    # its whole-quarter literal path in the former and its per-pixel one (edge pairs) in the latter
+    order = rng.permutation(m).astype(np.int32)
+    regular_only = order[order < m - len(irregular)]
+    lists = [order, order, regular_only, regular_only]
+    payload = np.concatenate(lists).astype(np.int32)
+    lens = np.array([len(x) for x in lists])
+    end = np.cumsum(lens).astype(np.int32)
+    start = (end - lens).astype(np.int32)
     records = np.zeros((m, 12), np.float32)
     records[:, 0:2] = uv
     records[:, 2:5] = conic[:, 0:3]
@@ -720,14 +737,15 @@ def _blend_case_by_hand(seed=0):
     records[:, 6] = alpha
     records[:, 7:10] = color
     records[:, 10] = xyz_cam[:, 2]
+    records[:, 11] = util.decision_band_log2(conic, alpha)
     return dict(W=W, H=H, m=m, uv=uv, conic=conic, alpha=alpha, color=color, xyz_cam=xyz_cam,
                 payload=payload, start=start, end=end, records=records, first_irregular=m_regular + m_edge)
 
 
-@pytest.mark.parametrize("with_masks", [True, False])
+@pytest.mark.parametrize("magnitude", [True, False])
 @pytest.mark.parametrize("persistent", ["1", "0"])
 def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries(
-        oracle32, oracle64, with_masks, persistent, monkeypatch):
+        oracle32, oracle64, magnitude, persistent, monkeypatch):
     """gs_blend_fwd + gs_blend_bwd through the C ABI on hand-made records: irregular conics take the
     guarded literal path in BOTH directions and pairs on the alpha = 1/255 edge are re-decided with
     the reference's backward arithmetic (R.py:626-669, utils.py:331-345), so num_affected_pixels
@@ -744,12 +762,16 @@ def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries
     last = torch.empty(H, W, dtype=torch.int32, device=dev)
     count = torch.empty(H, W, dtype=torch.int32, device=dev)
     k = payload.shape[0]
-    masks = torch.zeros(4 * k, dtype=torch.uint8, device=dev) if with_masks else None
+    masks = torch.zeros(4 * k, dtype=torch.uint8, device=dev)
+    flags = torch.full((4 * 4,), 7, dtype=torch.uint8, device=dev)       # every byte must be written
+    scratch = torch.full((int(capi.lib.gs_blend_bwd_scratch_bytes(H, W)),), 3, dtype=torch.uint8, device=dev)
     st = torch.cuda.current_stream().cuda_stream
     capi.check(capi.lib.gs_blend_fwd(H, W, start.data_ptr(), end.data_ptr(), payload.data_ptr(),
                                      records.data_ptr(), image.data_ptr(), depth.data_ptr(), acc.data_ptr(),
-                                     last.data_ptr(), count.data_ptr(), 0,
-                                     masks.data_ptr() if with_masks else None, k, st), "gs_blend_fwd")
+                                     last.data_ptr(), count.data_ptr(), 0, masks.data_ptr(), k,
+                                     flags.data_ptr(), st), "gs_blend_fwd")
+    fl = flags.cpu().numpy().reshape(4, 4)
+    assert set(fl.ravel().tolist()) <= {0, 1} and fl[:2].all() and not fl[2:].any()
     f = oracle32.blend_fwd(H, W, c["start"], c["end"], c["payload"], c["uv"], c["xyz_cam"], c["conic"],
                            c["alpha"], c["color"])
     got = dict(rasterized_image=image.cpu().numpy(), rasterized_depth=depth.cpu().numpy(),
@@ -773,8 +795,9 @@ def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries
     on_image = torch.empty(H, W, 2, device=dev)
     capi.check(capi.lib.gs_blend_bwd(H, W, start.data_ptr(), end.data_ptr(), payload.data_ptr(),
                                      records.data_ptr(), tt(g).data_ptr(), acc.data_ptr(), last.data_ptr(),
-                                     splat_grads.data_ptr(), on_image.data_ptr(),
-                                     masks.data_ptr() if with_masks else None, k, st), "gs_blend_bwd")
+                                     splat_grads.data_ptr(), on_image.data_ptr() if magnitude else None,
+                                     masks.data_ptr(), k, flags.data_ptr(), scratch.data_ptr(), st),
+               "gs_blend_bwd")
     torch.cuda.synchronize()
     sg = splat_grads.cpu().numpy()
     aff = sg[:, 10].astype(np.int64)
@@ -786,10 +809,23 @@ def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries
     assert np.isfinite(sg).all()
     want = np.concatenate([b64["grad_uv"], b64["cov_buf"], b64["color_buf"], b64["grad_logit"][:, None],
                            b64["magnitude_grad_viewspace"][:, None]], axis=1)
-    l2, mx = util.grad_error(want, sg[:, :10])
-    rows = util.row_error_summary(want, sg[:, :10])
+    cols = 10 if magnitude else 9
+    l2, mx = util.grad_error(want[:, :cols], sg[:, :cols])
+    rows = util.row_error_summary(want[:, :cols], sg[:, :cols])
     print(f"hand-made blend case: rel-l2 {l2:.2e} max-col-norm {mx:.2e} per-row p99.9 {rows['p999']:.1e}")
     assert l2 <= 1e-4 and mx <= 1e-4
-    l2, mx = util.grad_error(b64["magnitude_grad_viewspace_on_image"].reshape(-1, 2),
-                             on_image.cpu().numpy().reshape(-1, 2))
-    assert l2 <= 1e-4 and mx <= 1e-4
+    if magnitude:
+        l2, mx = util.grad_error(b64["magnitude_grad_viewspace_on_image"].reshape(-1, 2),
+                                 on_image.cpu().numpy().reshape(-1, 2))
+        assert l2 <= 1e-4 and mx <= 1e-4
+    else:
+        assert np.all(sg[:, 9] == 0)
+    # the scratch holds the list of pixels the literal pass re-did ({count, entries}; bit 31 = a pixel of
+    # a quarter left whole to it): this case must have exercised both kinds of literal work
+    fix = scratch.cpu().numpy().view(np.uint32)
+    entries = fix[1:1 + int(fix[0])]
+    whole = entries[entries >> 31 == 1] & 0x7fffffff
+    edge = entries[entries >> 31 == 0]
+    assert len(np.unique(entries & 0x7fffffff)) == len(entries)          # every pixel at most once
+    assert len(whole) == 2 * 256 and set((whole // W // 16 * 2 + whole % W // 16).tolist()) == {0, 1}
+    assert len(edge) > 20 and set((edge // W // 16 * 2 + edge % W // 16).tolist()) <= {2, 3}

@@ -29,6 +29,16 @@ def oracle_forward(oracle, scene, near=0.8, far=1000.0, scale=100.0, rgb_only=Fa
                           scene.height, near, far, scale, rgb_only)
 
 
+def tile_offsets_of(st) -> torch.Tensor:
+    """accumulated_num_overlap_tiles (R.py:913-922) of a forward state: the kernel's own scan if it was
+    asked for, else (inputs beyond the packed scan's capacity) the exclusive cumsum of the tile counts."""
+    buf = st.buffers
+    if buf.has("tile_offsets"):
+        return buf.view("tile_offsets", st.m)
+    counts = buf.view("num_tiles", st.m).to(torch.int64)
+    return torch.cumsum(counts, 0) - counts
+
+
 def literal_unsorted_keys(st, width):
     """The reference's unsorted keys / payload in emission order (R.py:131-172), from the literal
     emission entry point run on the forward's per-point buffers."""
@@ -38,11 +48,18 @@ def literal_unsorted_keys(st, width):
     pay = torch.empty(max(st.k, 1), dtype=torch.int32, device=dev)
     if st.k > 0:
         buf = st.buffers
+        offsets = tile_offsets_of(st).contiguous()
         _capi.check(_capi.lib.gs_emit_keys(buf.ptr("bbox"), buf.ptr("depth_key"),
-                                           buf.ptr("tile_offsets"), st.m, st.k, width,
+                                           offsets.data_ptr(), st.m, st.k, width,
                                            keys.data_ptr(), pay.data_ptr(),
                                            torch.cuda.current_stream(dev).cuda_stream), "gs_emit_keys")
     return keys[:st.k], pay[:st.k]
+
+
+def _scan_fits(scene) -> bool:
+    """gs_project_cull_sh produces the tile-offset scan only while n x tiles-per-image < 2^35."""
+    n = scene.point_cloud.shape[0]
+    return n < (1 << 27) and n * (scene.width // 16) * (scene.height // 16) < (1 << 35)
 
 
 def cuda_forward_state(scene, near=0.8, far=1000.0, scale=100.0):
@@ -55,7 +72,8 @@ def cuda_forward_state(scene, near=0.8, far=1000.0, scale=100.0):
     cam = CameraInfo(camera_intrinsics=t["camera_intrinsics"], camera_height=scene.height,
                      camera_width=scene.width, camera_id=0)
     st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"], t["point_invalid_mask"],
-                            t["point_object_id"], t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam)
+                            t["point_object_id"], t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
+                            debug_outputs=True, offsets_output=_scan_fits(scene))
     torch.cuda.synchronize()
     return st
 
@@ -79,7 +97,7 @@ def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False
         st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"],
                                 t["point_invalid_mask"], t["point_object_id"],
                                 t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
-                                keep_unsorted=True)
+                                keep_unsorted=True, debug_outputs=True, offsets_output=_scan_fits(scene))
     finally:
         impl.KEY_PIPELINE = saved
     if st.unsorted_keys is None and st.k > 0:
@@ -96,7 +114,7 @@ def cuda_forward_stages(scene, near=0.8, far=1000.0, scale=100.0, rgb_only=False
         point_color=np_(buf.view("color", m)),
         point_radii=np_(buf.view("radii", m)),
         num_overlap_tiles=np_(buf.view("num_tiles", m)),
-        accumulated_num_overlap_tiles=np_(buf.view("tile_offsets", m)),
+        accumulated_num_overlap_tiles=np_(tile_offsets_of(st)),
         records=np_(buf.view("records", m)),
         point_in_camera_sort_key=np_(st.sorted_keys()),
         point_offset_with_sort_key=np_(st.payload),
@@ -201,3 +219,19 @@ def row_error_summary(ref: np.ndarray, got: np.ndarray) -> dict:
         return dict(rows=0, p50=0.0, p99=0.0, p999=0.0, max=0.0)
     return dict(rows=int(e.size), p50=float(np.percentile(e, 50)), p99=float(np.percentile(e, 99)),
                 p999=float(np.percentile(e, 99.9)), max=float(e.max()))
+
+
+def decision_band_log2(conic_and_rescale: np.ndarray, alpha: np.ndarray) -> np.ndarray:
+    """The 12th float of a splat record as gs_project_cull_sh writes it (include/gs_b200.h, gs_blend_bwd):
+    s = log2(255 peak / (1 + band)), band = min(3e-6 + 6e-7 tau (1 + rho) / (1 - rho), 0.02); 0 for records
+    that are irregular or can never reach alpha = 1/255."""
+    c = np.asarray(conic_and_rescale, np.float64)
+    a, b, cc = c[:, 0], c[:, 1], c[:, 2]
+    peak = c[:, 3] * np.asarray(alpha, np.float64)
+    with np.errstate(all="ignore"):
+        ok = (peak > 0) & (a > 0) & (cc > 0) & (a * cc > b * b) & np.isfinite(a + b + cc + peak)
+        rho = np.minimum(np.sqrt(b * b / (a * cc)), 0.9999)
+        tau = np.maximum(2.0 * np.log(255.0 * peak), 0.0)
+        band = np.minimum(3e-6 + 6e-7 * tau * (1 + rho) / (1 - rho), 0.02)
+        s = np.log2(255.0 * peak / (1.0 + band))
+    return np.where(ok, s, 0.0).astype(np.float32)

@@ -44,19 +44,21 @@ def main():
     on_image = torch.zeros(h, w, 2, dtype=torch.float32, device=dev)
     stream = torch.cuda.current_stream().cuda_stream
     lib = _capi.lib
+    scratch = torch.empty(int(lib.gs_blend_bwd_scratch_bytes(h, w)), dtype=torch.uint8, device=dev)
 
     def fwd():
         _capi.check(lib.gs_blend_fwd(h, w, st.tile_start.data_ptr(), st.tile_end.data_ptr(), st.payload.data_ptr(),
                                      st.buffers.ptr("records"), st.image.data_ptr(), st.depth.data_ptr(),
                                      st.acc_alpha.data_ptr(), st.last.data_ptr(), st.count.data_ptr(), 0,
-                                     st.cell_masks.data_ptr(), st.k, stream), "gs_blend_fwd")
+                                     st.cell_masks.data_ptr(), st.k, st.quarter_flags.data_ptr(), stream),
+                    "gs_blend_fwd")
 
     def bwd(magnitude):
         _capi.check(lib.gs_blend_bwd(h, w, st.tile_start.data_ptr(), st.tile_end.data_ptr(), st.payload.data_ptr(),
                                      st.buffers.ptr("records"), g.data_ptr(), st.acc_alpha.data_ptr(),
                                      st.last.data_ptr(), grads.data_ptr(),
                                      on_image.data_ptr() if magnitude else None, st.cell_masks.data_ptr(), st.k,
-                                     stream), "gs_blend_bwd")
+                                     st.quarter_flags.data_ptr(), scratch.data_ptr(), stream), "gs_blend_bwd")
 
     def time_it(fn):
         ts = []
@@ -72,6 +74,15 @@ def main():
         return round(float(np.median(ts)), 4)
 
     out = {"workload": args.workload, "m": st.m, "k": st.k}
+    bwd(False)
+    torch.cuda.synchronize()
+    fix = scratch.view(torch.int32)
+    entries = fix[1:1 + int(fix[0])]
+    out["pixels_flagged_ambiguous"] = int((entries >= 0).sum())
+    out["pixels_flagged_whole_quarter"] = int((entries < 0).sum())
+    os.environ["GS_BWD_FIXUP"] = "0"
+    out["bwd_without_literal_pass_ms"] = time_it(lambda: bwd(False))
+    os.environ.pop("GS_BWD_FIXUP")
     for mode in ("1", "0"):
         os.environ["GS_BLEND_PERSISTENT"] = mode
         tag = "persistent" if mode == "1" else "cta_per_tile"
