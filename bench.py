@@ -122,17 +122,6 @@ def make_views_spread(num_views: int, seed: int = 9):
     return q.astype(np.float32), t.astype(np.float32)
 
 
-def lpt_assignment(costs, world):
-    """Longest-processing-time-first: views by decreasing cost, each to the least loaded rank."""
-    loads = [0.0] * world
-    mine = [[] for _ in range(world)]
-    for v in sorted(range(len(costs)), key=lambda i: -costs[i]):
-        r = min(range(world), key=lambda i: (loads[i], len(mine[i])))
-        mine[r].append(v)
-        loads[r] += costs[v]
-    return mine, loads
-
-
 def peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -789,8 +778,9 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         dist.all_reduce(shared)
         stats = shared.cpu().numpy()
     m_view, k_view = stats[:, 0], stats[:, 1]
-    costs = (k_view + 3.0 * m_view).tolist()        # stage times at C4: ~0.07 ns per list entry, ~0.23 ns per point
-    assignment, loads = lpt_assignment(costs, world)
+    from taichi_3d_gaussian_splatting_b200.distributed import assign_views_lpt, view_cost
+    costs = [view_cost(m, k) for m, k in zip(m_view, k_view)]
+    assignment, loads = assign_views_lpt(costs, world)
     rr_loads = [sum(costs[v] for v in round_robin[r]) for r in range(world)]
     mine = assignment[rank]
     steps = max(3, min(args.steps, 6))

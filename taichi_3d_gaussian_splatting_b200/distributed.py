@@ -1,9 +1,14 @@
 """View-sharded multi-GPU step (new functionality; the reference is single-GPU, README.md:325).
 
-The path shards over camera views: every rank holds the whole point cloud, renders the views
-`v = rank, rank + world, ...` of a batch forward+backward with the single-view operator, and the one
-exchange step is the sum of the N x 3 + N x 56 gradient over ranks (`all_reduce`, NCCL over NVLink on
-GPUs; gloo in the CPU tests).  One process per GPU, launched with torch.distributed.run.
+The path shards over camera views: every rank holds the whole point cloud, renders its share of a
+batch's views forward+backward with the single-view operator, and the one exchange step is the sum of
+the N x 56 + N x 3 gradient over ranks (`all_reduce`, NCCL over NVLink on GPUs; gloo in the CPU
+tests).  One process per GPU, launched with torch.distributed.run.
+
+Which rank renders which view: round robin (`views_of_rank`) by default; with per-view costs from a
+previous pass (`assign_views_lpt`, longest-processing-time first on K + 3 M: list entries and visible
+points) the ranks' loads differ by a few per cent instead of by the spread of the views, and a step
+ends when its SLOWEST rank does.
 
 The operator normalises the quaternion columns of the visible points in place (reference
 R.py:264-266), and different ranks see different points, so the replicas would drift apart by
@@ -13,7 +18,7 @@ step (16 B per point, against 236 B per point for the gradient all-reduce).
 from __future__ import annotations
 
 from dataclasses import dataclass
-from typing import Any, Callable, List, Optional, Sequence
+from typing import Any, Callable, List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -22,6 +27,26 @@ import torch.distributed as dist
 def views_of_rank(num_views: int, rank: int, world: int) -> List[int]:
     """Indices of the views rank `rank` renders: v = rank (mod world)."""
     return list(range(rank, num_views, world))
+
+
+def view_cost(num_points_in_camera: float, num_keys: float) -> float:
+    """Work of one view forward+backward, in list-entry equivalents: the blend and binning kernels go
+    with the K list entries, the projection and the per-point backward with the M visible points (stage
+    times at 2M points, 976x544: ~0.07 ns per entry, ~0.23 ns per point)."""
+    return float(num_keys) + 3.0 * float(num_points_in_camera)
+
+
+def assign_views_lpt(costs: Sequence[float], world: int) -> Tuple[List[List[int]], List[float]]:
+    """Longest-processing-time-first: views by decreasing cost, each to the least loaded rank.
+    Deterministic, so every rank computes the same assignment from the same (all-reduced) costs.
+    Returns (views per rank, load per rank)."""
+    loads = [0.0] * world
+    mine: List[List[int]] = [[] for _ in range(world)]
+    for v in sorted(range(len(costs)), key=lambda i: (-costs[i], i)):
+        r = min(range(world), key=lambda i: (loads[i], len(mine[i]), i))
+        mine[r].append(v)
+        loads[r] += costs[v]
+    return mine, loads
 
 
 @dataclass
@@ -42,17 +67,26 @@ class ViewShardedTrainerStep:
     def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
                  loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
                  group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True,
-                 rasteriser: Any = None, lanes: int = 4):
+                 rasteriser: Any = None, lanes: int = 4, balance: bool = False):
         """rasteriser: the GaussianPointCloudRasterisation module `render` calls, if the step should
         use its fused accumulation (`accumulate_gradients_into`): every view's backward then adds
         into one flat N x 59 buffer (no per-view zero fill, no AccumulateGrad pass) and the exchange
-        is ONE all-reduce of that buffer.
+        is ONE all-reduce of that buffer.  Gradients that reach the two parameters from loss terms
+        that do not pass through the rasteriser (the scale regulariser of LossFunction) arrive through
+        autograd as usual and are added into the buffer before the exchange.  (Do not combine the fused
+        path with LossFunction(fold_regulariser_gradient=True): its tensor hook rides on the
+        rasteriser's gradient, which the fused path never hands to autograd.)
         lanes: with the fused accumulation on a CUDA device, this rank's views are spread over that many
         CUDA streams (view j on lane j mod lanes).  The views are independent (their gradients meet only
         in the RED adds into the flat buffer), the blend kernels are issue-bound and the key pipeline is
         latency / HBM bound, so views in flight fill each other's idle slots (+8 % with 2 lanes, +10 % with 4 at 1M points,
         1920x1088; tools/exp_two_streams.py).  The sum order of the gradient then varies from run to
-        run (differences of 1e-7 relative)."""
+        run (differences of 1e-7 relative).  A backward_valid_point_hook of the rasteriser runs on its
+        view's lane, concurrently with other views' hooks: it must only ADD into shared state with
+        atomics (AdaptiveControllerAccumulators.update does); a hook with plain read-modify-write on
+        shared tensors needs lanes=1.
+        balance: assign the views by longest-processing-time-first on the costs measured in the previous
+        call (the rasteriser's `last_forward_info`; needs `rasteriser`) instead of round robin."""
         self.lanes = max(1, int(lanes))
         self._streams: List[Any] = []
         self.render = render
@@ -60,9 +94,20 @@ class ViewShardedTrainerStep:
         self.group = group
         self.sync_quaternions = sync_quaternions
         self.rasteriser = rasteriser
+        self.balance = bool(balance) and rasteriser is not None
         self._flat: Optional[torch.Tensor] = None
+        self._costs: Optional[List[float]] = None   # per view, from the previous call
 
-    def _run_on_lanes(self, point_cloud, point_cloud_features, views, mine) -> torch.Tensor:
+    def _render_view(self, point_cloud, point_cloud_features, views, v, costs):
+        image = self.render(point_cloud, point_cloud_features, views[v])
+        if costs is not None:
+            info = self.rasteriser.last_forward_info
+            costs[v] = view_cost(info.get("num_points_in_camera", 0), info.get("num_keys", 0))
+        loss = self.loss_fn(image, views[v])
+        loss.backward()
+        return loss.detach()
+
+    def _run_on_lanes(self, point_cloud, point_cloud_features, views, mine, costs) -> torch.Tensor:
         dev = point_cloud.device
         cur = torch.cuda.current_stream(dev)
         while len(self._streams) < self.lanes:
@@ -77,10 +122,7 @@ class ViewShardedTrainerStep:
         for j, v in enumerate(mine):
             lane = j % self.lanes
             with torch.cuda.stream(self._streams[lane]):
-                image = self.render(point_cloud, point_cloud_features, views[v])
-                loss = self.loss_fn(image, views[v])
-                loss.backward()
-                totals[lane] += loss.detach()
+                totals[lane] += self._render_view(point_cloud, point_cloud_features, views, v, costs)
         for s in self._streams:
             done = torch.cuda.Event()
             done.record(s)
@@ -103,7 +145,11 @@ class ViewShardedTrainerStep:
                 point_cloud_features.detach()[:, 0:4] = q
         point_cloud.grad = None
         point_cloud_features.grad = None
-        mine = views_of_rank(len(views), rank, world)
+        if self.balance and self._costs is not None and len(self._costs) == len(views):
+            mine = assign_views_lpt(self._costs, world)[0][rank]
+        else:
+            mine = views_of_rank(len(views), rank, world)
+        costs = [0.0] * len(views) if self.balance else None
         total = torch.zeros((), dtype=torch.float32, device=point_cloud.device)
         fused = self.rasteriser is not None
         if fused:
@@ -118,17 +164,24 @@ class ViewShardedTrainerStep:
         use_lanes = fused and self.lanes > 1 and point_cloud.is_cuda and len(mine) > 1
         try:
             if use_lanes:
-                total = total + self._run_on_lanes(point_cloud, point_cloud_features, views, mine)
+                total = total + self._run_on_lanes(point_cloud, point_cloud_features, views, mine, costs)
             else:
-                for v in mine:
-                    image = self.render(point_cloud, point_cloud_features, views[v])
-                    loss = self.loss_fn(image, views[v])
-                    loss.backward()          # accumulates across this rank's views
-                    total = total + loss.detach()
+                for v in mine:     # autograd accumulates across this rank's views (not fused)
+                    total = total + self._render_view(point_cloud, point_cloud_features, views, v, costs)
         finally:
             if fused:
                 self.rasteriser.accumulate_gradients_into(None, None)
+        if costs is not None:
+            shared = torch.tensor(costs, dtype=torch.float64, device=point_cloud.device)
+            if world > 1:
+                dist.all_reduce(shared, group=self.group)   # every view was rendered by exactly one rank
+            self._costs = shared.tolist()
         if fused:
+            # whatever reached the parameters through autograd (loss terms outside the rasteriser)
+            if point_cloud.grad is not None:
+                gx.add_(point_cloud.grad)
+            if point_cloud_features.grad is not None:
+                gf.add_(point_cloud_features.grad)
             if world > 1:
                 dist.all_reduce(self._flat, group=self.group)
                 dist.all_reduce(total, group=self.group)

@@ -19,6 +19,21 @@ def test_views_of_rank_partition():
             assert seen == list(range(nv))
 
 
+def test_assign_views_lpt_partitions_and_balances():
+    import numpy as np
+    from taichi_3d_gaussian_splatting_b200.distributed import assign_views_lpt, view_cost
+    rng = np.random.default_rng(0)
+    costs = [view_cost(m, k) for m, k in zip(rng.uniform(6e5, 2e6, 64), rng.uniform(4e6, 1e7, 64))]
+    for world in (1, 2, 4, 8):
+        mine, loads = assign_views_lpt(costs, world)
+        assert sorted(v for r in mine for v in r) == list(range(64))
+        assert all(abs(loads[r] - sum(costs[v] for v in mine[r])) < 1e-6 * loads[r] for r in range(world))
+        rr = [sum(costs[v] for v in views_of_rank(64, r, world)) for r in range(world)]
+        assert max(loads) <= max(rr) + 1e-9
+        assert max(loads) / (sum(loads) / world) < 1.02          # 64 views over <= 8 ranks: within 2 %
+    assert assign_views_lpt(costs, 4) == assign_views_lpt(list(costs), 4)   # deterministic
+
+
 def _render(xyz, feat, view):
     # differentiable, view dependent, and like the operator it normalises the q columns in place
     # for the points this view "sees"

@@ -608,6 +608,103 @@ def test_view_sharded_step_on_two_lanes_matches_one_lane():
             assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
 
 
+@pytest.mark.parametrize("n", [5001, 5002, 5003])
+def test_fused_step_with_point_counts_that_are_not_multiples_of_four(n):
+    """The flat N x 59 buffer of the fused step holds the N x 56 block first, so its rows stay 16-byte
+    aligned for every N (they are added with red.global.add.v4); with the N x 3 block first any N that is
+    not a multiple of 4 faulted."""
+    from taichi_3d_gaussian_splatting_b200.distributed import ViewShardedTrainerStep
+    scene = make_scene(n, 128, 96, seed=31, scale_factor=0.03)
+    g = torch.from_numpy(np.random.default_rng(2).uniform(0, 1, (96, 128, 3)).astype(np.float32)).cuda()
+    views = [(0.0, 0.0), (0.02, -0.01), (-0.03, 0.02)]
+    grads = []
+    for fused in (False, True):
+        ras = _module()
+        t = util.scene_tensors(scene, requires_grad=True)
+
+        def render(xyz, feat, view, t=t, ras=ras):
+            t["t_pointcloud_camera"] = torch.tensor([[view[0], view[1], 0.0]], device="cuda")
+            return _call(ras, scene, t, band=3)[0]
+
+        step = ViewShardedTrainerStep(render, lambda image, view: (image * g).sum(),
+                                      rasteriser=ras if fused else None, lanes=2)
+        step(t["point_cloud"], t["point_cloud_features"], views)
+        torch.cuda.synchronize()
+        if fused:
+            assert t["point_cloud_features"].grad.data_ptr() % 16 == 0
+        grads.append((t["point_cloud"].grad.cpu().numpy(), t["point_cloud_features"].grad.cpu().numpy()))
+    for a, b in zip(grads[0], grads[1]):
+        l2, mx = util.grad_error(a, b)
+        assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
+    with pytest.raises(ValueError, match="16-byte"):
+        ras = _module()
+        flat = torch.zeros(n * 59 + 1, device="cuda")
+        ras.accumulate_gradients_into(flat[1 + 56 * n:].view(n, 3), flat[1:1 + 56 * n].view(n, 56))
+
+
+def test_fused_step_keeps_gradients_from_outside_the_rasteriser():
+    """A loss term on the parameters that does not pass through the rasteriser (the reference trainer's
+    scale regulariser, LossFunction.py:40-52) must survive the fused step's in-place accumulation."""
+    from taichi_3d_gaussian_splatting_b200.distributed import ViewShardedTrainerStep
+    scene = make_scene(4000, 128, 96, seed=33, scale_factor=0.03)
+    g = torch.from_numpy(np.random.default_rng(3).uniform(0, 1, (96, 128, 3)).astype(np.float32)).cuda()
+    views = [(0.0, 0.0), (0.02, -0.01)]
+    grads = []
+    for fused in (False, True):
+        ras = _module()
+        t = util.scene_tensors(scene, requires_grad=True)
+
+        def render(xyz, feat, view, t=t, ras=ras):
+            t["t_pointcloud_camera"] = torch.tensor([[view[0], view[1], 0.0]], device="cuda")
+            return _call(ras, scene, t, band=3)[0]
+
+        def loss_fn(image, view, t=t):
+            reg = torch.exp(t["point_cloud_features"][:, 4:7]).norm(dim=1).mean() + t["point_cloud"].pow(2).mean()
+            return (image * g).sum() + 2.0 * reg
+
+        step = ViewShardedTrainerStep(render, loss_fn, rasteriser=ras if fused else None, lanes=1)
+        step(t["point_cloud"], t["point_cloud_features"], views)
+        grads.append((t["point_cloud"].grad.cpu().numpy(), t["point_cloud_features"].grad.cpu().numpy()))
+    assert np.abs(grads[0][1][:, 4:7]).max() > 0
+    for a, b in zip(grads[0], grads[1]):
+        l2, mx = util.grad_error(a, b)
+        assert l2 <= 1e-5 and mx <= 1e-5, (l2, mx)
+
+
+def test_densification_statistics_with_views_on_concurrent_lanes():
+    """The backward hook of every view runs on its view's lane; AdaptiveControllerAccumulators.update adds
+    with atomics, so views whose hooks run concurrently lose no update (integer statistics exactly equal,
+    float sums equal up to the order of the additions)."""
+    from taichi_3d_gaussian_splatting_b200.distributed import ViewShardedTrainerStep
+    from taichi_3d_gaussian_splatting_b200.GaussianPointAdaptiveController import AdaptiveControllerAccumulators
+    scene = make_scene(30000, 256, 160, seed=35, scale_factor=0.02)
+    g = torch.from_numpy(np.random.default_rng(4).uniform(0, 1, (160, 256, 3)).astype(np.float32)).cuda()
+    views = [(0.004 * i, -0.003 * i) for i in range(8)]
+    stats = []
+    for lanes in (1, 4):
+        t = util.scene_tensors(scene, requires_grad=True)
+        acc = AdaptiveControllerAccumulators(t["point_cloud"].shape[0], "cuda")
+        ras = _module(hook=acc.update)
+
+        def render(xyz, feat, view, t=t, ras=ras):
+            t["t_pointcloud_camera"] = torch.tensor([[view[0], view[1], 0.0]], device="cuda")
+            return _call(ras, scene, t, band=3)[0]
+
+        step = ViewShardedTrainerStep(render, lambda image, view: (image * g).sum(), rasteriser=ras, lanes=lanes)
+        for _ in range(3):
+            step(t["point_cloud"], t["point_cloud_features"], views)
+        torch.cuda.synchronize()
+        stats.append({k: v.cpu().numpy() for k, v in vars(acc).items() if isinstance(v, torch.Tensor)})
+    assert len(stats[0]) >= 6
+    for key, a in stats[0].items():
+        b = stats[1][key]
+        if np.issubdtype(a.dtype, np.integer):
+            assert np.array_equal(a, b), key
+        else:
+            assert np.allclose(a, b, rtol=1e-4, atol=1e-7 * max(1.0, np.abs(a).max())), key
+    assert stats[0]["accumulated_num_in_camera"].max() == 24
+
+
 def test_persistent_blend_launch_equals_one_cta_per_tile(monkeypatch):
     """The backward blend's persistent launch (warps pull (tile, part) units from a per-stream counter
     that the last warp re-arms) against the plain one-CTA-per-tile launch (GS_BLEND_PERSISTENT=0):
