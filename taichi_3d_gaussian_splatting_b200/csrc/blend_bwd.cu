@@ -266,10 +266,13 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             if (live) {
                 // the forward's culling bits for these cells: plane q of the tile's 8x8 quarters, two
                 // bits (upper / lower 8x4 cell) per entry
+                // (a quarter none of whose cells still reaches this entry may never have had its byte
+                // written by the forward: it is not read)
                 unsigned m = 0u;
 #pragma unroll
                 for (int h = 0; h < kCells / 2; ++h)
-                    m |= ((unsigned)__ldg(cell_masks + (q0 + h) * mask_stride + my_i) & 3u) << (2 * h);
+                    if ((live >> (2 * h)) & 3u)
+                        m |= ((unsigned)__ldg(cell_masks + (q0 + h) * mask_stride + my_i) & 3u) << (2 * h);
                 my_mask = live & m;
             }
         }
