@@ -22,6 +22,7 @@
 //   12 M + 8 E (pass 1) + 8 E + 4 K (pass 2)  ~ 0.11 GB   against
 //   8 K (emit) + 2 x 16 K (two sort passes) + 4 K (ranges) ~ 0.54 GB for the pair-sort chain.
 // The result (sorted payload, tile_start, tile_end) is bit-identical to that chain's.
+#include <algorithm>
 #include <cstdlib>
 
 #include "gs_common.cuh"
@@ -131,20 +132,23 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
     __shared__ uint32_t s_warp[kBinBlock / 32];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    // input entries of this pass; the grid is sized for a capacity, the surplus CTAs leave at once
+    // input entries of this pass (pass 2: known on the device only, so the host sizes the grid for what
+    // fits the machine and every CTA takes chunks, in order, until they run out)
     const long long n = (kPass == 1) ? m : (long long)ws[kWsColTotal];
-    if ((long long)blockIdx.x * kBinChunk >= n) return;
+    // bin bases: the scans of bin_count_kernel's histograms
+    const uint32_t bin_excl = ws[(kPass == 1 ? kWsColExcl : kWsRowExcl) + tid];
+    if (kPass == 2) s_colbase[tid] = ws[kWsColExcl + tid];
+    for (;;) {
+    __syncthreads();  // the previous chunk's shared state is no longer read
     if (tid == 0) {
         s_ticket = atomicAdd(ws + kWsTickets + (kPass - 1), 1u);
         s_nbound = 0;
     }
     for (int i = tid; i < kBinWords * nb; i += kBinBlock) smem[i] = 0ull;
-    // bin bases: the scans of bin_count_kernel's histograms
-    const uint32_t bin_excl = ws[(kPass == 1 ? kWsColExcl : kWsRowExcl) + tid];
-    if (kPass == 2) s_colbase[tid] = ws[kWsColExcl + tid];
     __syncthreads();
     const long long chunk = s_ticket;
     const long long chunk_start = chunk * kBinChunk;
+    if (chunk_start >= n) return;  // uniform: no chunk left
     const bool last = chunk_start + kBinChunk >= n;
 
     // ---- load: warp w of round j owns the 32 consecutive entries of mask word j * 8 + w ------------
@@ -308,6 +312,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
             }
         }
     }
+    }  // next chunk
 }
 
 // tile t's list is [starts[t], starts[t + 1]); an empty tile reads (0, 0) as in the reference, whose
@@ -388,11 +393,38 @@ extern "C" int gs_bin_tiles(const int32_t *order, const uint16_t *bbox, int64_t 
     // split measures the same or slightly better with direct stores and the occupancy the staging buffer
     // would cost (C2 0.164 against 0.169 ms for the whole call, C5 1.581 against 1.591 ms)
     const bool stage1 = false;
-    bin_pass_kernel<1><<<(unsigned)chunks1, kBinBlock, bin_smem(cols, stage1), st>>>(
+    // persistent grids: as many CTAs as are resident at once (a CTA that cannot start before others have
+    // finished would only find the ticket counter exhausted); pass 2's chunk count is a capacity, most of
+    // which is usually not there (C2: 3 125 chunks of 11 952, C5: 27 k of 181 k)
+    struct Resident {
+        int cols = -1, rows = -1, ctas1 = 0, ctas2 = 0;
+    };
+    static Resident cache[64];
+    static std::mutex cache_mu;
+    Resident res;
+    {
+        std::lock_guard<std::mutex> lock(cache_mu);
+        Resident &c = cache[dev & 63];
+        if (c.cols != cols || c.rows != rows) {
+            int sms = 0, per_sm1 = 0, per_sm2 = 0;
+            GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+            GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm1, bin_pass_kernel<1>, kBinBlock,
+                                                                      bin_smem(cols, stage1)));
+            GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm2, bin_pass_kernel<2>, kBinBlock,
+                                                                      bin_smem(rows, true)));
+            c.cols = cols; c.rows = rows;
+            c.ctas1 = sms * std::max(per_sm1, 1);
+            c.ctas2 = sms * std::max(per_sm2, 1);
+        }
+        res = c;
+    }
+    const int64_t grid1 = std::min<int64_t>(chunks1, res.ctas1);
+    const int64_t grid2 = std::min<int64_t>(chunks2, res.ctas2);
+    bin_pass_kernel<1><<<(unsigned)grid1, kBinBlock, bin_smem(cols, stage1), st>>>(
         order, boxes, m, nullptr, (unsigned long long *)entries, nullptr, ws, status1, cols, rows, nullptr,
         stage1 ? 1 : 0);
     GS_LAUNCH_CHECK();
-    bin_pass_kernel<2><<<(unsigned)chunks2, kBinBlock, bin_smem(rows, true), st>>>(
+    bin_pass_kernel<2><<<(unsigned)grid2, kBinBlock, bin_smem(rows, true), st>>>(
         nullptr, nullptr, m, (const unsigned long long *)entries, nullptr, payload, ws, status2, cols, rows,
         starts, 1);
     GS_LAUNCH_CHECK();

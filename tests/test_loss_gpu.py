@@ -194,3 +194,34 @@ def test_folded_regulariser_gradient_matches_the_autograd_one():
     want = 2.5 * (1e-3 * wmat.astype(np.float64))
     want[:, 4:7] += 2.5 * o["grad_scale"]
     assert np.allclose(results[1][1], want, rtol=2e-5, atol=1e-8)
+
+
+def test_against_the_package_the_reference_imports():
+    """The pin the loss row is missing: the reference computes SSIM with
+    pytorch_msssim.ssim(pred, gt, data_range=1, size_average=True) (LossFunction.py:4,30-31), a third-party
+    package that is not vendored.  Where it is importable this test compares gs_loss_fwd / gs_loss_bwd with
+    that exact call + autograd; where it is not (this image: neither here nor on the GPU box, and nothing
+    can be installed) it SKIPS -- it never passes vacuously -- and the row stays "parity unpinned"."""
+    try:
+        import pytorch_msssim
+    except ImportError:
+        pytest.skip("pytorch_msssim is not installed on this box: loss parity against the package the "
+                    "reference imports stays unpinned (oracle = restatement of its published algorithm)")
+    if "ti_shim" in (getattr(pytorch_msssim, "__file__", "") or ""):
+        pytest.skip("only the test stand-in of pytorch_msssim is importable here, not the package")
+    img, gt = _images(96, 128, 77)
+    pred = torch.from_numpy(img).cuda().requires_grad_(True)
+    target = torch.from_numpy(gt).cuda()
+    lam = 0.2
+    x = torch.clamp(pred, 0, 1).permute(2, 0, 1)
+    l1 = torch.abs(x - target).mean()
+    ld = 1 - pytorch_msssim.ssim(x.unsqueeze(0), target.unsqueeze(0), data_range=1, size_average=True)
+    want = (1 - lam) * l1 + lam * ld
+    want.backward()
+    want_grad = pred.grad.clone()
+    pred.grad = None
+    got, got_l1, got_ld = _module(lambda_value=lam, enable_regularization=False).forward_rasterised(pred, target)
+    got.backward()
+    print("pytorch_msssim", getattr(pytorch_msssim, "__version__", "?"), "loss", float(want), float(got))
+    assert abs(float(got) - float(want)) <= LOSS_TOL and abs(float(got_ld) - float(ld)) <= LOSS_TOL
+    assert float((pred.grad - want_grad).abs().max()) <= GRAD_TOL * float(want_grad.abs().max())
