@@ -28,6 +28,7 @@ extern "C" {
 #define GS_OK 0
 #define GS_E_INVALID (-1)   /* bad argument (null pointer, W or H not a multiple of 16, ...) */
 #define GS_E_CAPACITY (-2)  /* a count exceeds what the int32 index contract allows */
+#define GS_E_STATIC_LIMIT (-3) /* a *_static entry point was asked for more than its fixed scratch holds */
 
 #define GS_TILE 16          /* R.py:27-28 */
 #define GS_BOUNDARY_TILES 3 /* R.py:26 */
@@ -84,6 +85,28 @@ int gs_project_cull_sh(const float *xyz, float *features, const int8_t *invalid_
                        float *alpha, float *color, float *radii, int32_t *num_tiles,
                        int64_t *tile_offsets, float *records, uint16_t *bbox,
                        int32_t *depth_key, int64_t *totals, void *workspace, void *stream);
+
+/*
+ * gs_project_cull_sh without a caller-allocated workspace, for callers that cannot allocate (code under
+ * CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
+ * REFERENCE.  Same arguments, meaning and results as
+ * gs_project_cull_sh minus `workspace`: the look-back scratch lives in a file-scope device array of the
+ * library (8 bytes per 256 points, ~512 KiB; every GPU that loads the library holds it until exit),
+ * whose device address is resolved once per device.  Calls no cudaMalloc / cudaFree / allocating
+ * routine.  n > GS_PROJECT_STATIC_MAX_POINTS returns GS_E_STATIC_LIMIT.  All calls on a device share the
+ * array; each call clears what it uses first (in stream order), so calls in sequence are independent,
+ * but calls that OVERLAP on the GPU (two streams without a dependency) race on it -- serialise them.
+ */
+#define GS_PROJECT_STATIC_MAX_POINTS (1ll << 24)
+int gs_project_cull_sh_static(const float *xyz, float *features, const int8_t *invalid_mask,
+                              const int32_t *object_id, int64_t n, const float *intrinsics /*3x3*/,
+                              const float *q_cam_pc, const float *t_cam_pc, int n_obj,
+                              float near_plane, float far_plane, int width, int height,
+                              float depth_to_sort_key_scale,
+                              int32_t *ids, float *point_uv, float *point_in_camera, float *conic,
+                              float *alpha, float *color, float *radii, int32_t *num_tiles,
+                              int64_t *tile_offsets, float *records, uint16_t *bbox,
+                              int32_t *depth_key, int64_t *totals, void *stream);
 
 /*
  * Key/payload emission.  Replaces generate_point_sort_key_by_num_overlap_tiles (R.py:131-172).

@@ -481,3 +481,46 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
+
+// ---- no-allocation variant ---------------------------------------------------------------------------
+// gs_project_cull_sh_static: the same pass with its look-back scratch in a file-scope device array
+// instead of a caller-allocated workspace, for callers that cannot allocate (CUDA graph capture, serving
+// loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the array (~512 KiB) until exit.  The
+// array's name is a host-side stand-in in host code, not a device address: the launcher takes its
+// address with cudaGetSymbolAddress once per device, with that device current.  All calls on a device
+// share the array: gs_project_cull_sh clears the words a call uses before its kernel (stream-ordered
+// memset), so nothing of the previous call is read, but two calls that OVERLAP on the GPU (different
+// streams, no dependency) race on it.
+static constexpr long long kStaticMaxPoints = GS_PROJECT_STATIC_MAX_POINTS;
+static constexpr long long kStaticWords = (kStaticMaxPoints + kProjBlock - 1) / kProjBlock + 2;
+static __device__ __align__(256) unsigned long long g_project_static_scratch[kStaticWords];
+
+extern "C" int gs_project_cull_sh_static(const float *xyz, float *features, const int8_t *invalid_mask,
+                                         const int32_t *object_id, int64_t n, const float *intrinsics,
+                                         const float *q_cam_pc, const float *t_cam_pc, int n_obj,
+                                         float near_plane, float far_plane, int width, int height,
+                                         float depth_to_sort_key_scale, int32_t *ids, float *point_uv,
+                                         float *point_in_camera, float *conic, float *alpha, float *color,
+                                         float *radii, int32_t *num_tiles, int64_t *tile_offsets,
+                                         float *records, uint16_t *bbox, int32_t *depth_key,
+                                         int64_t *totals, void *stream)
+{
+    if (n > kStaticMaxPoints) return GS_E_STATIC_LIMIT;
+    static_assert(sizeof(g_project_static_scratch) >= (size_t)(kStaticWords * 8), "scratch size");
+    static void *address[64];
+    static GsPerDeviceOnce resolved;
+    int dev = 0;
+    if (resolved.need(dev)) {
+        if (dev < 0 || dev >= 64) return GS_E_INVALID;
+        void *ptr = nullptr;
+        GS_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_project_static_scratch));  // of the CURRENT device
+        if (!ptr) return GS_E_INVALID;
+        address[dev] = ptr;
+        resolved.mark(dev);
+    }
+    return gs_project_cull_sh(xyz, features, invalid_mask, object_id, n, intrinsics, q_cam_pc, t_cam_pc,
+                              n_obj, near_plane, far_plane, width, height, depth_to_sort_key_scale, ids,
+                              point_uv, point_in_camera, conic, alpha, color, radii, num_tiles,
+                              tile_offsets, records, bbox, depth_key, totals, address[dev], stream);
+}
