@@ -216,6 +216,9 @@ def stage_bytes(n, m, k, tiles, hw, info):
         "zero_fill": 48 * m,
         "blend_bwd": 44 * k + 28 * hw + 8 * hw + 44 * m,
         "point_bwd": 280 * m + 232 * m,
+        # per STEP of V views: every feature row in, every gradient row out, per view the slot map and,
+        # per visible point, 48 bytes of reduced gradients + 12 of camera-space position
+        "point_bwd_batch": (224 + 236) * n + VIEWS_PER_RANK * (4 * n + 60 * m),
     }
 
 
@@ -330,11 +333,25 @@ class Rig:
         self.lanes = max(1, lanes)
         self.lane_streams = [torch.cuda.Stream(dev) for _ in range(self.lanes)] if self.lanes > 1 else []
 
-    def batch_mode(self, on: bool):
-        if on:
-            self.ras.accumulate_gradients_into(self.gx, self.gf)
-        else:
-            self.ras.accumulate_gradients_into(None, None)
+    def begin_step(self):
+        """The views that follow are a gradient batch: their backward parks the reduced screen-space
+        gradients, `finish_step` turns all of them into point gradients in one pass over the points."""
+        self.ras.begin_gradient_batch(self.gx, self.gf)
+
+    def finish_step(self, dist, world, chunks=8):
+        """Per-point backward of the step's views (gs_point_bwd_batch) and, for world > 1, the exchange:
+        the pass is cut into `chunks` point ranges and the all-reduce of a range is started as soon as the
+        range is written, so it overlaps the computation of the following ranges."""
+        pending = []
+
+        def after_chunk(index, first, count):
+            pending.append(dist.all_reduce(self.gf[first:first + count], async_op=True))
+            pending.append(dist.all_reduce(self.gx[first:first + count], async_op=True))
+
+        self.ras.end_gradient_batch(chunks if world > 1 else 1, after_chunk if world > 1 else None)
+        for work in pending:
+            work.wait()
+        self.xyz.grad, self.feat.grad = self.gx, self.gf
 
     def forward(self, q, t):
         Ras = self.Ras
@@ -430,9 +447,7 @@ def run_b200(args):
         return ((step * world + rank) * VIEWS_PER_RANK + j) % NUM_VIEWS
 
     def finish_step():
-        if world > 1:  # the one exchange step of the path: sum the N x 59 gradient over ranks
-            dist.all_reduce(flat)
-        xyz.grad, feat.grad = gx, gf
+        rig.finish_step(dist, world)   # per-point backward of the 8 views + the exchange of the N x 59 gradient
 
     def resident_view(i):
         def per_view(j, stream):
@@ -441,13 +456,13 @@ def run_b200(args):
         return per_view
 
     def step_resident(i):
-        flat.zero_()
+        rig.begin_step()
         total = rig.run_views(VIEWS_PER_RANK, resident_view(i))
         finish_step()
         return total
 
     def step_resident_single_stream(i):  # the instrumented pass: per-stage CUDA events need one stream
-        flat.zero_()
+        rig.begin_step()
         total = rig.run_views(VIEWS_PER_RANK, resident_view(i), use_lanes=False)
         finish_step()
         return total
@@ -475,7 +490,7 @@ def run_b200(args):
         uploads[g] = (q, t, wt_stage[slot], ev)
 
     def step_e2e(i):
-        flat.zero_()
+        rig.begin_step()
         if next_upload[0] < i * VIEWS_PER_RANK or not uploads:   # first call: nothing prefetched yet
             copy_stream.wait_stream(torch.cuda.current_stream(dev))
             uploads.clear()
@@ -544,7 +559,6 @@ def run_b200(args):
     prof = StageProfiler()
     prio = bool(args.priority_sections) and lanes > 1
     impl.PRIORITY_SECTIONS = prio
-    rig.batch_mode(True)
     timed(step_resident, 0, warmup)            # untimed warm-up (allocator, module load)
     sampler.start()
     ms_resident = timed(step_resident, args.steps, 0)
@@ -562,7 +576,6 @@ def run_b200(args):
     impl.PRIORITY_SECTIONS = False
     info = dict(ras.last_forward_info)
     # the drop-in figure and the two render figures (no batch extension, no lanes)
-    rig.batch_mode(False)
     single_iters = args.steps * VIEWS_PER_RANK
     ms_single = timed(step_single_view, single_iters, 2 * warmup)
     xyz.grad = feat.grad = None
@@ -572,7 +585,6 @@ def run_b200(args):
     if args.timeline and rank == 0:
         from torch.profiler import ProfilerActivity, profile
         impl.PRIORITY_SECTIONS = prio
-        rig.batch_mode(True)
         step_resident(0)
         torch.cuda.synchronize()
         with profile(activities=[ProfilerActivity.CUDA, ProfilerActivity.CPU]) as tl:
@@ -580,7 +592,6 @@ def run_b200(args):
             step_resident(2)
             torch.cuda.synchronize()
         impl.PRIORITY_SECTIONS = False
-        rig.batch_mode(False)
         tl.export_chrome_trace(args.timeline)
 
     # release the headline workload before the C4 leg allocates its own
@@ -668,7 +679,8 @@ def run_b200(args):
     depth_bits, tile_bits = int(info["depth_bits"]), int(info["tile_bits"])
     if info.get("key_pipeline") == "binned":
         # pose, project | point sort: hist+scan+passes | bin: count, columns, rows, ranges |
-        # blend_fwd, blend_bwd, point_bwd   (memsets are not counted)
+        # blend_fwd, blend_bwd + its literal pass   (memsets are not counted; + 1 per step: the batched
+        # per-point backward, added below)
         launches_per_step = 2 + (2 + (depth_bits + 7) // 8) + 4 + 3
     elif info.get("key_pipeline") == "depth_first":
         # pose, project | point sort: hist+scan+passes | emit | pair sort: hist+scan+passes |
@@ -686,8 +698,9 @@ def run_b200(args):
         "config": {"workload": args.workload, "points": n, "width": w, "height": h, "sh_degree": 3,
                    "near": 0.8, "far": 1000.0, "depth_to_sort_key_scale": 100.0,
                    "visible_points": m, "keys": k, "views": NUM_VIEWS,
-                   "step": f"{VIEWS_PER_RANK} views forward+backward per rank, gradients summed in "
-                           "place, one all-reduce; an iteration (it) = one view forward+backward",
+                   "step": f"{VIEWS_PER_RANK} views forward+backward per rank as one gradient batch (per-point "
+                           "chain rule of all views in one pass over the points), the N x 59 gradient all-reduced "
+                           "in 8 point ranges that overlap that pass; an iteration (it) = one view forward+backward",
                    "views_per_rank_per_step": VIEWS_PER_RANK,
                    "lanes": lanes, "priority_sections": prio,
                    "lanes_note": f"view j of a step runs on CUDA stream j mod {lanes}; `stages` / `roofline` are "
@@ -718,7 +731,7 @@ def run_b200(args):
                               "around the timed forwards under no_grad) with gaussian_point_render.py's frame "
                               "handling: pose uploaded from pinned host memory, clamp(image * 255).byte() copied "
                               "to host memory with a blocking copy every frame"},
-        "gpu_launches": launches_per_step * VIEWS_PER_RANK * args.steps,
+        "gpu_launches": (launches_per_step * VIEWS_PER_RANK + 1) * args.steps,
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline, "stages": stages,
         "c4": c4,
     }
@@ -732,7 +745,6 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     ranks (STRONG scaling: E(G) = T(1, 64 views) / (G T(G, 64 views)))."""
     name = "c4_2m_976x544"
     rig = Rig(torch, impl, dev, name, lanes)
-    rig.batch_mode(True)
     q_np, t_np = make_views_spread(C4_VIEWS)
     q_dev, t_dev = torch.from_numpy(q_np).to(dev), torch.from_numpy(t_np).to(dev)
     stats = np.zeros((C4_VIEWS, 2), np.float64)   # per view: M, K of the last recorded pass
@@ -748,10 +760,9 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         return rig.run_views(len(mine), per_view)
 
     def step(mine, exchange=True):
-        rig.flat.zero_()
+        rig.begin_step()
         total = render_views(mine)
-        if world > 1 and exchange:
-            dist.all_reduce(rig.flat)
+        rig.finish_step(dist, world if exchange else 1)
         return total
 
     def timed(fn, steps):
@@ -770,8 +781,9 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     # pass 0 (round robin) measures every view's work; from then on the views are dealt out by
     # longest-processing-time-first on it, the way a trainer would use the previous epoch's numbers
     round_robin = [list(range(r, C4_VIEWS, world)) for r in range(world)]
-    rig.flat.zero_()
+    rig.begin_step()
     render_views(round_robin[rank], record=True)
+    rig.finish_step(dist, 1)
     torch.cuda.synchronize()
     if world > 1:
         shared = torch.from_numpy(stats).to(dev)
@@ -825,7 +837,6 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         "view_keys_min_max": [int(k_view.min()), int(k_view.max())],
         "verify": verify,
     }
-    rig.batch_mode(False)
     rig.xyz.grad = rig.feat.grad = None
     del rig
     torch.cuda.empty_cache()

@@ -73,6 +73,8 @@ int gs_inverse_pose(const float *q_pc_cam, const float *t_pc_cam, int n_obj, flo
  *   and tile_offsets [n] i64 (exclusive scan of num_tiles), which only gs_emit_keys reads.  With
  *   tile_offsets the look-back word packs 27 bits of points and 35 bits of tiles: GS_E_CAPACITY if
  *   n >= 2^27 or n x (tiles per image) >= 2^35 (a carry could otherwise corrupt the point count).
+ *   slot_of_point [n] i32 (NULLABLE): for EVERY point its position in the visible list, or -1 -- the
+ *   inverse of ids, read by gs_point_bwd_batch.
  * features: 16-byte aligned (rows are fetched with cp.async.bulk); GS_E_INVALID otherwise.
  * workspace: gs_project_workspace_bytes(n) bytes, contents irrelevant on entry.
  */
@@ -84,7 +86,8 @@ int gs_project_cull_sh(const float *xyz, float *features, const int8_t *invalid_
                        int32_t *ids, float *point_uv, float *point_in_camera, float *conic,
                        float *alpha, float *color, float *radii, int32_t *num_tiles,
                        int64_t *tile_offsets, float *records, uint16_t *bbox,
-                       int32_t *depth_key, int64_t *totals, void *workspace, void *stream);
+                       int32_t *depth_key, int32_t *slot_of_point, int64_t *totals, void *workspace,
+                       void *stream);
 
 /*
  * gs_project_cull_sh without a caller-allocated workspace, for callers that cannot allocate (code under
@@ -106,7 +109,8 @@ int gs_project_cull_sh_static(const float *xyz, float *features, const int8_t *i
                               int32_t *ids, float *point_uv, float *point_in_camera, float *conic,
                               float *alpha, float *color, float *radii, int32_t *num_tiles,
                               int64_t *tile_offsets, float *records, uint16_t *bbox,
-                              int32_t *depth_key, int64_t *totals, void *stream);
+                              int32_t *depth_key, int32_t *slot_of_point, int64_t *totals,
+                              void *stream);
 
 /*
  * Key/payload emission.  Replaces generate_point_sort_key_by_num_overlap_tiles (R.py:131-172).
@@ -248,6 +252,33 @@ int gs_point_bwd(const float *xyz, const float *features, const int32_t *object_
                  float high_order_color_factor, float *grad_xyz, float *grad_features,
                  float *hook_grad_xyz, float *hook_grad_features, float *hook_grad_viewspace,
                  float *hook_magnitude, int32_t *hook_num_affected, int accumulate, void *stream);
+
+/*
+ * The per-point chain rule of a whole batch of views in one pass over the points (the view-sharded
+ * step; not in the reference, which renders one view per step).  Equivalent to
+ * gs_point_bwd with accumulate != 0 called once per view on zeroed buffers, but every point's feature
+ * row is read once, what depends on the view is summed in registers, and the gradient rows of ALL points
+ * of the range [first_point, first_point + num_points) are STORED once (zeros for points no view sees):
+ * no zero fill, no read-modify-write.  Calls over disjoint ranges are independent, so a step can be cut
+ * into chunks that are exchanged (all-reduced) while the next chunk is computed.
+ * views_device: DEVICE array of num_views gs_view_t (16-byte aligned), one per view of the batch, all
+ * of whose pointers are device pointers into that view's forward / backward-blend state.
+ * Hook outputs are not produced: a batch with a backward hook uses gs_point_bwd per view.
+ */
+typedef struct gs_view_t {
+    const int32_t *slot_of_point;  /* [n]   gs_project_cull_sh: position in the visible list or -1 */
+    const float *point_in_camera;  /* [m,3] gs_project_cull_sh */
+    const float *splat_grads;      /* [m,12] gs_blend_bwd */
+    const float *intrinsics;       /* [3,3] */
+    const float *q_cam_pc;         /* [n_obj,4] gs_inverse_pose */
+    const float *t_pc_cam;         /* [n_obj,3] the INPUT translation (R.py:731-732,749) */
+    int64_t reserved[2];           /* pads the record to 64 bytes */
+} gs_view_t;
+int gs_point_bwd_batch(const float *xyz, const float *features, const int32_t *object_id,
+                       int64_t first_point, int64_t num_points, const gs_view_t *views_device,
+                       int num_views, int color_max_sh_band, float q_factor, float s_factor,
+                       float alpha_factor, float color_factor, float high_order_color_factor,
+                       float *grad_xyz, float *grad_features, void *stream);
 
 /* ---------------------------------------------------------------------------------------------
  * Loss front-end: what runs between the rasteriser's image and the

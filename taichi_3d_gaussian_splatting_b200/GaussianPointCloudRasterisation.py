@@ -115,14 +115,16 @@ class _PointBuffers:
         ("records", torch.float32, _REC),
         ("bbox", torch.int16, 4),
         ("depth_key", torch.int32, 1),
+        ("slot_of_point", torch.int32, 1),
     )
     CORE = ("ids", "point_in_camera", "records", "bbox", "depth_key")
     HOOK = ("point_uv", "num_tiles")
     DEBUG = ("conic", "alpha", "color", "radii")
     OFFSETS = ("tile_offsets",)
+    SLOTS = ("slot_of_point",)   # the inverse of ids, for gs_point_bwd_batch
 
     def __init__(self, n: int, device: torch.device, hook: bool = False, debug: bool = False,
-                 offsets: bool = False):
+                 offsets: bool = False, slots: bool = False):
         self.n = n
         wanted = set(self.CORE)
         if hook or debug:
@@ -131,6 +133,8 @@ class _PointBuffers:
             wanted |= set(self.DEBUG)
         if offsets:
             wanted |= set(self.OFFSETS)
+        if slots:
+            wanted |= set(self.SLOTS)
         self.offsets: Dict[str, int] = {}
         off = 0
         for name, dtype, cols in self.FIELDS:
@@ -233,6 +237,8 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
         self.config = config
         self.last_forward_info: Dict[str, object] = {}
         self._accumulate_into = None
+        self._batch: Optional[_GradientBatch] = None
+        self._has_hook = backward_valid_point_hook is not None
         outer = self
 
         class _module_function(torch.autograd.Function):
@@ -253,7 +259,8 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                                     point_object_id, q_pointcloud_camera, t_pointcloud_camera,
                                     camera_info,
                                     keep_cell_masks=ctx.needs_input_grad[0] or ctx.needs_input_grad[1],
-                                    hook_outputs=backward_valid_point_hook is not None)
+                                    hook_outputs=backward_valid_point_hook is not None,
+                                    slots_output=outer._batch is not None)
                 outer.last_forward_info = out.info
                 ctx.set_materialize_grads(False)
                 ctx.camera_info = camera_info
@@ -261,6 +268,7 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                 # where this call's gradients go is fixed NOW: a later accumulate_gradients_into()
                 # (or another user of the module) must not redirect a backward already recorded
                 ctx.accumulate_into = outer._accumulate_into
+                ctx.batch = outer._batch
                 # the outputs must not be reachable from ctx (output -> grad_fn -> ctx cycle)
                 image, depth, count = out.image, out.depth, out.count
                 out.image = out.depth = out.count = None
@@ -281,7 +289,7 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                         t_pointcloud_camera, ctx.camera_info, ctx.color_max_sh_band,
                         grad_rasterized_image, backward_valid_point_hook,
                         GaussianPointCloudRasterisation.BackwardValidPointHookInput,
-                        accumulate_into=ctx.accumulate_into)
+                        accumulate_into=ctx.accumulate_into, batch=ctx.batch)
                 return grad_pointcloud, grad_pointcloud_features, None, None, None, None, None, None
 
         self._module_function = _module_function
@@ -310,6 +318,34 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                              "red.global.add.v4.f32); put the N x 56 block first in a flat buffer")
         self._accumulate_into = (grad_point_cloud, grad_point_cloud_features)
 
+    def begin_gradient_batch(self, grad_point_cloud: torch.Tensor, grad_point_cloud_features: torch.Tensor) -> None:
+        """Extension for multi-view batches, deferred form (not in the reference).  Until
+        `end_gradient_batch`, every backward of this module runs its blend backward only and PARKS the
+        view's reduced screen-space gradients (48 bytes per visible point); no gradient is returned to
+        autograd for the two point inputs.  `end_gradient_batch` then runs the per-point chain rule of
+        ALL parked views in one pass over the points (gs_point_bwd_batch) and STORES the summed gradient
+        rows into the two buffers ([N,3] and [N,56], float32, contiguous, 16-byte aligned; they need not
+        be zeroed): each feature row is read once per batch instead of once per view, and nothing is
+        read-modify-written.  Not available with a backward_valid_point_hook (its payload is per view)."""
+        if self._has_hook:
+            raise ValueError("gradient batches do not produce the per-view hook payload: use "
+                             "accumulate_gradients_into with a backward_valid_point_hook")
+        self.accumulate_gradients_into(grad_point_cloud, grad_point_cloud_features)   # validates
+        self._accumulate_into = None
+        self._batch = _GradientBatch(grad_point_cloud, grad_point_cloud_features)
+
+    def end_gradient_batch(self, chunks: int = 1,
+                           after_chunk: Optional[Callable[[int, int, int], None]] = None) -> int:
+        """Runs the parked views' per-point backward on the current stream (the caller has made it wait
+        for the streams the views ran on) and leaves batch mode.  With chunks > 1 the points are cut into
+        that many id ranges, one launch each, and `after_chunk(index, first_point, num_points)` is called
+        after each launch -- e.g. to start the all-reduce of that range while the next one is computed.
+        Returns the number of views that were in the batch."""
+        batch, self._batch = self._batch, None
+        if batch is None:
+            raise RuntimeError("end_gradient_batch without begin_gradient_batch")
+        return batch.finish(self.config, max(1, int(chunks)), after_chunk)
+
     def forward(self, input_data: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput"):
         camera_info = input_data.camera_info
         assert camera_info.camera_width % TILE_WIDTH == 0
@@ -324,6 +360,69 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
             camera_info,
             input_data.color_max_sh_band,
         )
+
+
+class _GradientBatch:
+    """The views parked between begin_gradient_batch and end_gradient_batch."""
+
+    def __init__(self, grad_point_cloud: torch.Tensor, grad_point_cloud_features: torch.Tensor):
+        self.grad_xyz, self.grad_features = grad_point_cloud, grad_point_cloud_features
+        self.views = []       # per view: the tensors gs_view_t points into (kept alive until finish)
+        self.common = None    # (xyz, features, object_id, colour band) -- the same for every view
+
+    def park(self, pointcloud, pointcloud_features, point_object_id, color_max_sh_band, st, splat_grads,
+             t_pc) -> None:
+        common = (pointcloud.data_ptr(), pointcloud_features.data_ptr(), point_object_id.data_ptr(),
+                  int(color_max_sh_band), pointcloud.shape[0])
+        if self.common is None:
+            self.common = common
+            self.tensors = (pointcloud, pointcloud_features, point_object_id)
+        elif common != self.common:
+            raise ValueError("the views of a gradient batch must share the point tensors and the colour band")
+        buf = st.buffers
+        # small copies, so that the view's large forward buffers can be released now
+        self.views.append(dict(slot=buf.view("slot_of_point", st.n).clone(),
+                               pic=buf.view("point_in_camera", max(st.m, 1)).clone(),
+                               sg=splat_grads, K=st.intrinsics, q_cam=st.q_cam, t_pc=t_pc))
+
+    def finish(self, cfg, chunks: int, after_chunk) -> int:
+        n = self.grad_xyz.shape[0]
+        dev = self.grad_xyz.device
+        cur = torch.cuda.current_stream(dev)
+        if self.common is None:            # no view on this rank: the gradient is zero
+            self.grad_xyz.zero_()
+            self.grad_features.zero_()
+            if after_chunk is not None:
+                after_chunk(0, 0, n)
+            return 0
+        xyz, features, object_id = self.tensors
+        rows = []
+        for v in self.views:
+            rows.append([v["slot"].data_ptr(), v["pic"].data_ptr(), v["sg"].data_ptr(), v["K"].data_ptr(),
+                         v["q_cam"].data_ptr(), v["t_pc"].data_ptr(), 0, 0])
+            for t in v.values():
+                t.record_stream(cur)       # produced on the view's lane, consumed here
+        table = torch.tensor(rows, dtype=torch.int64).pin_memory().to(dev, non_blocking=True)
+        band = self.common[3]
+        chunks = max(1, min(chunks, (n + 127) // 128))
+        per = ((n + chunks - 1) // chunks + 127) // 128 * 128
+        first, index = 0, 0
+        while first < n:
+            count = min(per, n - first)
+            _capi.check(_lib.gs_point_bwd_batch(
+                xyz.detach().contiguous().data_ptr(), features.detach().data_ptr(),
+                object_id.contiguous().data_ptr(), first, count, table.data_ptr(), len(rows), band,
+                float(cfg.grad_q_factor), float(cfg.grad_s_factor), float(cfg.grad_alpha_factor),
+                float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
+                self.grad_xyz.data_ptr(), self.grad_features.data_ptr(), cur.cuda_stream), "gs_point_bwd_batch")
+            if after_chunk is not None:
+                after_chunk(index, first, count)
+            first += count
+            index += 1
+        _mark("point_bwd_batch")
+        num = len(self.views)
+        self.views = []
+        return num
 
 
 _READBACK: Dict[int, tuple] = {}  # device index -> (side stream, pinned int64[2])
@@ -396,7 +495,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
                   q_pointcloud_camera, t_pointcloud_camera, camera_info,
                   keep_unsorted: bool = False, keep_cell_masks: bool = False,
                   hook_outputs: bool = False, debug_outputs: bool = False,
-                  offsets_output: bool = False) -> _ForwardState:
+                  offsets_output: bool = False, slots_output: bool = False) -> _ForwardState:
     """hook_outputs: also produce point_uv / num_overlap_tiles (a backward hook will show them);
     debug_outputs: every reference-named per-point buffer (tests); offsets_output: the exclusive scan
     of the tile counts even when the key pipeline in use does not read it (tests)."""
@@ -440,7 +539,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
     # the per-point scan of the tile counts is read by the literal key emission only (binned falls back
     # to depth_first, never to literal)
     buf = _PointBuffers(n, dev, hook=hook_outputs, debug=debug_outputs,
-                        offsets=offsets_output or not depth_first)
+                        offsets=offsets_output or not depth_first, slots=slots_output)
     st.buffers = buf
     totals = torch.empty(2, dtype=torch.int64, device=dev)
     ws = torch.empty(max(int(_lib.gs_project_workspace_bytes(n)), 16), dtype=torch.uint8, device=dev)
@@ -451,7 +550,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
         buf.ptr("ids"), buf.ptr("point_uv"), buf.ptr("point_in_camera"), buf.ptr("conic"),
         buf.ptr("alpha"), buf.ptr("color"), buf.ptr("radii"), buf.ptr("num_tiles"),
         buf.ptr("tile_offsets"), buf.ptr("records"), buf.ptr("bbox"), buf.ptr("depth_key"),
-        totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
+        buf.ptr("slot_of_point"), totals.data_ptr(), ws.data_ptr(), stream), "gs_project_cull_sh")
     _mark("project_cull_sh")
     after_project = torch.cuda.Event()
     after_project.record(s_small)
@@ -587,7 +686,7 @@ def _forward_impl(cfg, pointcloud, pointcloud_features, point_invalid_mask, poin
 
 def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, point_object_id,
                    t_pointcloud_camera, camera_info, color_max_sh_band, grad_rasterized_image,
-                   hook, hook_input_type, accumulate_into=None):
+                   hook, hook_input_type, accumulate_into=None, batch=None):
     CALL_COUNTS["backward"] += 1
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
@@ -595,7 +694,9 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     s_small = _companion_stream(s_big) if PRIORITY_SECTIONS else s_big
     stream = s_big.cuda_stream
     _mark("backward_begin")
-    if accumulate_into is not None:
+    if batch is not None:
+        grad_pointcloud = grad_features = None   # written by end_gradient_batch
+    elif accumulate_into is not None:
         grad_pointcloud, grad_features = accumulate_into
         if grad_pointcloud.shape[0] != n or grad_features.shape[0] != n:
             raise ValueError("accumulation buffers do not match the point cloud")
@@ -622,6 +723,11 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
                                   st.quarter_flags.data_ptr(), scratch.data_ptr(), stream),
                 "gs_blend_bwd")
     _mark("blend_bwd")
+    if batch is not None:
+        t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
+        batch.park(pointcloud, pointcloud_features, point_object_id, color_max_sh_band, st, splat_grads, t_pc)
+        _mark("park_view")
+        return None, None
     h_xyz = torch.empty(m, 3, dtype=torch.float32, device=dev) if want_hook else None
     h_feat = torch.empty(m, 56, dtype=torch.float32, device=dev) if want_hook else None
     h_view = torch.empty(m, 2, dtype=torch.float32, device=dev) if want_hook else None

@@ -14,7 +14,7 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = _build.LIB
 
-ABI_VERSION = 110
+ABI_VERSION = 111
 
 _p = C.c_void_p
 _i = C.c_int
@@ -39,10 +39,11 @@ SIGNATURES = {
     "gs_bin_tiles": (_i, [_p, _p, _l, _l, _i, _i, _p, _p, _p, _p, _p, _p]),
     "gs_inverse_pose": (_i, [_p, _p, _i, _p, _p, _p]),
     "gs_project_cull_sh": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
-                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+                                _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "gs_point_bwd_batch": (_i, [_p, _p, _p, _l, _l, _p, _i, _i, _f, _f, _f, _f, _f, _p, _p, _p]),
     # no workspace argument: its scratch is a file-scope device array of the library (no allocation)
     "gs_project_cull_sh_static": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
-                                       _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+                                       _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "gs_emit_keys": (_i, [_p, _p, _p, _l, _l, _i, _p, _p, _p]),
     "gs_sort_pairs": (_i, [_p, _p, _p, _p, _l, _i, _i, _p, C.POINTER(C.c_int), _p]),
     "gs_tile_ranges": (_i, [_p, _l, _p, _p, _i, _p]),

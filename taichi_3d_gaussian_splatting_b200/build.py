@@ -29,6 +29,7 @@ UNITS = {
     "blend_fwd.cu": ["-fmad=false"],
     "blend_bwd.cu": [],
     "point_bwd.cu": [],
+    "point_bwd_batch.cu": [],
     "loss.cu": [],
     "train_ops.cu": [],
 }

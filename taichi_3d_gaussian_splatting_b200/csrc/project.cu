@@ -72,6 +72,7 @@ struct ProjectParams {
     float *records;
     uint16_t *bbox;
     int32_t *depth_key;
+    int32_t *slot_of_point;  // nullable: [n] position of point i in the visible list, or -1
     long long *totals;
     unsigned long long *status;  // one word per block of 256 points, zero on entry
     unsigned int *ticket;        // zero on entry
@@ -377,13 +378,17 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
         }
     }
     __syncthreads();
-    if (!visible) return;
+    if (!visible) {
+        if (p.slot_of_point && i < p.n) p.slot_of_point[i] = -1;
+        return;
+    }
 
     unsigned long long my_excl = s_block_excl + warp_excl + (incl - mine);
     const long long idx = kOffsets ? (long long)(my_excl >> kPackShift) : (long long)my_excl;
 
     // what the path itself reads: ids, camera-space position, the packed record, bbox, depth key
     p.ids[idx] = (int32_t)i;
+    if (p.slot_of_point) p.slot_of_point[i] = (int32_t)idx;
     p.point_in_camera[3 * idx] = cx; p.point_in_camera[3 * idx + 1] = cy;
     p.point_in_camera[3 * idx + 2] = cz;
     // the reference-named per-point buffers (R.py:873-884), for callers that look at them (the
@@ -430,7 +435,7 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
                                   float *point_in_camera, float *conic, float *alpha, float *color,
                                   float *radii, int32_t *num_tiles, int64_t *tile_offsets,
                                   float *records, uint16_t *bbox, int32_t *depth_key,
-                                  int64_t *totals, void *workspace, void *stream)
+                                  int32_t *slot_of_point, int64_t *totals, void *workspace, void *stream)
 {
     if (n < 0 || width <= 0 || height <= 0 || width % kTile || height % kTile || n_obj <= 0)
         return GS_E_INVALID;
@@ -459,7 +464,7 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
     p.ids = ids; p.point_uv = point_uv; p.point_in_camera = point_in_camera; p.conic = conic;
     p.alpha = alpha; p.color = color; p.radii = radii; p.num_tiles = num_tiles;
     p.tile_offsets = (long long *)tile_offsets; p.records = records; p.bbox = bbox;
-    p.depth_key = depth_key; p.totals = (long long *)totals;
+    p.depth_key = depth_key; p.slot_of_point = slot_of_point; p.totals = (long long *)totals;
     int blocks = (int)((n + kProjBlock - 1) / kProjBlock);
     p.num_blocks = blocks;
     p.status = (unsigned long long *)workspace;
@@ -504,7 +509,7 @@ extern "C" int gs_project_cull_sh_static(const float *xyz, float *features, cons
                                          float *point_in_camera, float *conic, float *alpha, float *color,
                                          float *radii, int32_t *num_tiles, int64_t *tile_offsets,
                                          float *records, uint16_t *bbox, int32_t *depth_key,
-                                         int64_t *totals, void *stream)
+                                         int32_t *slot_of_point, int64_t *totals, void *stream)
 {
     if (n > kStaticMaxPoints) return GS_E_STATIC_LIMIT;
     static_assert(sizeof(g_project_static_scratch) >= (size_t)(kStaticWords * 8), "scratch size");
@@ -522,5 +527,6 @@ extern "C" int gs_project_cull_sh_static(const float *xyz, float *features, cons
     return gs_project_cull_sh(xyz, features, invalid_mask, object_id, n, intrinsics, q_cam_pc, t_cam_pc,
                               n_obj, near_plane, far_plane, width, height, depth_to_sort_key_scale, ids,
                               point_uv, point_in_camera, conic, alpha, color, radii, num_tiles,
-                              tile_offsets, records, bbox, depth_key, totals, address[dev], stream);
+                              tile_offsets, records, bbox, depth_key, slot_of_point, totals, address[dev],
+                              stream);
 }

@@ -67,7 +67,7 @@ class ViewShardedTrainerStep:
     def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
                  loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
                  group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True,
-                 rasteriser: Any = None, lanes: int = 4, balance: bool = False):
+                 rasteriser: Any = None, lanes: int = 4, balance: bool = False, exchange_chunks: int = 8):
         """rasteriser: the GaussianPointCloudRasterisation module `render` calls, if the step should
         use its fused accumulation (`accumulate_gradients_into`): every view's backward then adds
         into one flat N x 59 buffer (no per-view zero fill, no AccumulateGrad pass) and the exchange
@@ -86,7 +86,12 @@ class ViewShardedTrainerStep:
         atomics (AdaptiveControllerAccumulators.update does); a hook with plain read-modify-write on
         shared tensors needs lanes=1.
         balance: assign the views by longest-processing-time-first on the costs measured in the previous
-        call (the rasteriser's `last_forward_info`; needs `rasteriser`) instead of round robin."""
+        call (the rasteriser's `last_forward_info`; needs `rasteriser`) instead of round robin.
+        exchange_chunks: a rasteriser WITHOUT a backward hook runs the step as a gradient batch
+        (`begin_gradient_batch` / `end_gradient_batch`: the per-point chain rule of all the rank's views in
+        one pass over the points, gs_point_bwd_batch); with more than one rank that pass is cut into this
+        many point ranges and the all-reduce of a range starts as soon as the range is written, so that
+        the exchange overlaps the computation of the following ranges instead of following the step."""
         self.lanes = max(1, int(lanes))
         self._streams: List[Any] = []
         self.render = render
@@ -95,6 +100,7 @@ class ViewShardedTrainerStep:
         self.sync_quaternions = sync_quaternions
         self.rasteriser = rasteriser
         self.balance = bool(balance) and rasteriser is not None
+        self.exchange_chunks = max(1, int(exchange_chunks))
         self._flat: Optional[torch.Tensor] = None
         self._costs: Optional[List[float]] = None   # per view, from the previous call
 
@@ -152,15 +158,20 @@ class ViewShardedTrainerStep:
         costs = [0.0] * len(views) if self.balance else None
         total = torch.zeros((), dtype=torch.float32, device=point_cloud.device)
         fused = self.rasteriser is not None
+        batched = False
         if fused:
             n = point_cloud.shape[0]
             if self._flat is None or self._flat.numel() != n * 59 or self._flat.device != point_cloud.device:
                 self._flat = torch.empty(n * 59, dtype=torch.float32, device=point_cloud.device)
-            self._flat.zero_()
             # features first: their rows are added as 16-byte vectors and 224 n is a multiple of 16
             # for every n, 12 n is not
             gf, gx = self._flat[:56 * n].view(n, 56), self._flat[56 * n:].view(n, 3)
-            self.rasteriser.accumulate_gradients_into(gx, gf)
+            batched = point_cloud.is_cuda and not getattr(self.rasteriser, "_has_hook", True)
+            if batched:
+                self.rasteriser.begin_gradient_batch(gx, gf)      # every row is stored: no zero fill
+            else:
+                self._flat.zero_()
+                self.rasteriser.accumulate_gradients_into(gx, gf)
         use_lanes = fused and self.lanes > 1 and point_cloud.is_cuda and len(mine) > 1
         try:
             if use_lanes:
@@ -168,8 +179,12 @@ class ViewShardedTrainerStep:
             else:
                 for v in mine:     # autograd accumulates across this rank's views (not fused)
                     total = total + self._render_view(point_cloud, point_cloud_features, views, v, costs)
+        except BaseException:
+            if batched:
+                self.rasteriser._batch = None        # leave batch mode, drop the parked views
+            raise
         finally:
-            if fused:
+            if fused and not batched:
                 self.rasteriser.accumulate_gradients_into(None, None)
         if costs is not None:
             shared = torch.tensor(costs, dtype=torch.float64, device=point_cloud.device)
@@ -178,12 +193,33 @@ class ViewShardedTrainerStep:
             self._costs = shared.tolist()
         if fused:
             # whatever reached the parameters through autograd (loss terms outside the rasteriser)
-            if point_cloud.grad is not None:
-                gx.add_(point_cloud.grad)
-            if point_cloud_features.grad is not None:
-                gf.add_(point_cloud_features.grad)
+            extra_x, extra_f = point_cloud.grad, point_cloud_features.grad
+            if batched:
+                pending = []
+
+                def after_chunk(index, first, count):
+                    rows = slice(first, first + count)
+                    if extra_x is not None:
+                        gx[rows].add_(extra_x[rows])
+                    if extra_f is not None:
+                        gf[rows].add_(extra_f[rows])
+                    if world > 1:   # asynchronous: the next range is computed while this one is exchanged
+                        pending.append(dist.all_reduce(gf[rows], group=self.group, async_op=True))
+                        pending.append(dist.all_reduce(gx[rows], group=self.group, async_op=True))
+
+                try:
+                    self.rasteriser.end_gradient_batch(self.exchange_chunks if world > 1 else 1, after_chunk)
+                finally:
+                    for work in pending:
+                        work.wait()
+            else:
+                if extra_x is not None:
+                    gx.add_(extra_x)
+                if extra_f is not None:
+                    gf.add_(extra_f)
+                if world > 1:
+                    dist.all_reduce(self._flat, group=self.group)
             if world > 1:
-                dist.all_reduce(self._flat, group=self.group)
                 dist.all_reduce(total, group=self.group)
             point_cloud.grad, point_cloud_features.grad = gx, gf
             return StepResult(loss=total, num_local_views=len(mine))

@@ -64,10 +64,12 @@ def test_point_buffers_hold_only_what_was_asked_for():
     assert set(hook.offsets) == set(impl._PointBuffers.CORE) | {"point_uv", "num_tiles"}
     literal = impl._PointBuffers(1000, torch.device("cpu"), offsets=True)
     assert set(literal.offsets) == set(impl._PointBuffers.CORE) | {"tile_offsets"}
+    batch = impl._PointBuffers(1000, torch.device("cpu"), slots=True)
+    assert set(batch.offsets) == set(impl._PointBuffers.CORE) | {"slot_of_point"}
 
 
 def test_point_buffers_are_aligned_and_disjoint():
-    buf = impl._PointBuffers(1000, torch.device("cpu"), debug=True, offsets=True)
+    buf = impl._PointBuffers(1000, torch.device("cpu"), debug=True, offsets=True, slots=True)
     spans = []
     for name, dtype, cols in buf.FIELDS:
         size = 1000 * cols * torch.empty((), dtype=dtype).element_size()

@@ -575,6 +575,69 @@ def test_accumulate_gradients_into_sums_views():
         ras.accumulate_gradients_into(gx[:, :2], gf)
 
 
+@pytest.mark.parametrize("n,objects,band", [(5000, 1, 3), (7013, 3, 1)])
+def test_gradient_batch_equals_per_view_accumulation(n, objects, band):
+    """begin_gradient_batch / end_gradient_batch (gs_point_bwd_batch: the per-point chain rule of all
+    parked views in one pass over the points, rows stored once) against accumulate_gradients_into
+    (gs_point_bwd per view, rows added): the same sums up to the order of the additions -- for one and for
+    several point ranges, with a view that sees nothing, several objects, and poisoned output buffers
+    (every row of the range must be written, also those of points no view sees)."""
+    scene = make_scene(n, 128, 96, seed=21, scale_factor=0.03, num_objects=objects)
+    g = torch.from_numpy(np.random.default_rng(2).uniform(0, 1, (96, 128, 3)).astype(np.float32)).cuda()
+    poses = [(0.0, 0.0, 0.0), (0.02, -0.01, 0.0), (-0.03, 0.02, 0.1), (0.0, 0.0, 500.0)]   # the last sees nothing: the camera sits beyond every point
+    ras = _module()
+
+    def run(t, pose):
+        t["t_pointcloud_camera"] = t["t_base"] + torch.tensor([list(pose)], device="cuda")
+        image, _, _ = _call(ras, scene, t, band=band)
+        (image * g).sum().backward()
+
+    def fresh():
+        t = util.scene_tensors(scene, requires_grad=True)
+        t["t_base"] = t["t_pointcloud_camera"].clone()
+        return t
+
+    ref = fresh()
+    gx0 = torch.zeros(n, 3, device="cuda")
+    gf0 = torch.zeros(n, 56, device="cuda")
+    ras.accumulate_gradients_into(gx0, gf0)
+    for pose in poses:
+        run(ref, pose)
+    ras.accumulate_gradients_into(None, None)
+    assert ras.last_forward_info["num_points_in_camera"] == 0
+    for chunks in (1, 3):
+        t = fresh()
+        gx = torch.full((n, 3), float("nan"), device="cuda")
+        gf = torch.full((n, 56), float("nan"), device="cuda")
+        ras.begin_gradient_batch(gx, gf)
+        for pose in poses:
+            run(t, pose)
+        assert t["point_cloud"].grad is None and t["point_cloud_features"].grad is None
+        ranges = []
+        assert ras.end_gradient_batch(chunks, lambda i, first, count: ranges.append((i, first, count))) == len(poses)
+        torch.cuda.synchronize()
+        assert [r[0] for r in ranges] == list(range(len(ranges))) and len(ranges) == chunks
+        assert ranges[0][1] == 0 and sum(r[2] for r in ranges) == n
+        assert all(a[1] + a[2] == b[1] for a, b in zip(ranges, ranges[1:]))
+        assert torch.isfinite(gx).all() and torch.isfinite(gf).all()
+        for got, want in ((gx, gx0), (gf, gf0)):
+            l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
+            assert l2 <= 1e-5 and mx <= 1e-5, (chunks, l2, mx)
+        keep = {0: 1, 1: 4, 2: 9, 3: 16}[band]
+        for base in (8, 24, 40):
+            assert bool((gf[:, base + keep:base + 16] == 0).all())
+    # no view at all: the gradient of the batch is zero, and it is written
+    gx = torch.full((n, 3), float("nan"), device="cuda")
+    gf = torch.full((n, 56), float("nan"), device="cuda")
+    ras.begin_gradient_batch(gx, gf)
+    assert ras.end_gradient_batch() == 0
+    assert not gx.any() and not gf.any()
+    with pytest.raises(RuntimeError):
+        ras.end_gradient_batch()
+    with pytest.raises(ValueError, match="hook"):
+        _module(hook=lambda h: None).begin_gradient_batch(gx, gf)
+
+
 def test_view_sharded_step_on_two_lanes_matches_one_lane():
     """distributed.ViewShardedTrainerStep with the fused accumulation: six views spread over two CUDA
     streams give the gradient of the one-stream run (up to the order of the RED adds)."""

@@ -19,6 +19,7 @@ OUTPUTS = (  # name, columns, dtype; every per-point array is sized for n rows, 
     ("conic", 4, torch.float32), ("alpha", 1, torch.float32), ("color", 3, torch.float32),
     ("radii", 1, torch.float32), ("num_tiles", 1, torch.int32), ("tile_offsets", 1, torch.int64),
     ("records", 12, torch.float32), ("bbox", 4, torch.uint16), ("depth_key", 1, torch.int32),
+    ("slot_of_point", 1, torch.int32),   # the one array written for EVERY point (position or -1)
 )
 
 
@@ -79,7 +80,10 @@ def _compare(scene, dev, check_memory):
     m, k = (int(v) for v in ref["totals"].tolist())
     assert got["totals"].tolist() == [m, k]
     assert 0 < m < n and k > 0
+    assert torch.equal(ref["slot_of_point"], got["slot_of_point"]) and int((ref["slot_of_point"] >= 0).sum()) == m
     for name, cols, _ in OUTPUTS:
+        if name == "slot_of_point":
+            continue
         a, b = ref[name][: m * cols].view(torch.uint8), got[name][: m * cols].view(torch.uint8)
         assert torch.equal(a, b), f"{name} differs between gs_project_cull_sh and its _static variant"
         # neither writes past the M rows it reports
