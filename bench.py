@@ -77,6 +77,12 @@ def parse_args():
     ap.add_argument("--priority-sections", type=int, default=0,
                     help="with lanes > 1: the small kernels of a view (projection, sorts, binning, per-point "
                          "backward) run on a high-priority companion stream of the lane")
+    ap.add_argument("--exchange-chunks", type=int, default=1,
+                    help="N > 1: point ranges the per-point backward of a step is cut into, each all-reduced as "
+                         "soon as it is written (1 = one all-reduce after the pass)")
+    ap.add_argument("--c4-lanes", type=int, default=8,
+                    help="lanes of the c4 leg (its 976x544 views fill the machine less than a 1920x1088 one: "
+                         "8 lanes run a rank's 8 views 10 %% faster than 4, tools/exp_c4_rank_step.py)")
     ap.add_argument("--lanes", type=int, default=4,
                     help="CUDA streams the views of a step are spread over (view j on lane j mod L)")
     return ap.parse_args()
@@ -338,15 +344,20 @@ class Rig:
         gradients, `finish_step` turns all of them into point gradients in one pass over the points."""
         self.ras.begin_gradient_batch(self.gx, self.gf)
 
-    def finish_step(self, dist, world, chunks=8):
-        """Per-point backward of the step's views (gs_point_bwd_batch) and, for world > 1, the exchange:
-        the pass is cut into `chunks` point ranges and the all-reduce of a range is started as soon as the
-        range is written, so it overlaps the computation of the following ranges."""
+    def finish_step(self, dist, world, chunks=1):
+        """Per-point backward of the step's views (gs_point_bwd_batch) and, for world > 1, the exchange: one
+        all-reduce of the flat N x 59 buffer.  With chunks > 1 the pass is cut into that many point ranges
+        and the all-reduce of a range starts as soon as the range is written (measured, not adopted: at
+        N = 8 eight ranges cost 14.17 ms per step against 13.3 with one all-reduce -- sixteen small
+        collectives cost more than the 0.3 ms of computation they can hide behind)."""
         pending = []
 
         def after_chunk(index, first, count):
-            pending.append(dist.all_reduce(self.gf[first:first + count], async_op=True))
-            pending.append(dist.all_reduce(self.gx[first:first + count], async_op=True))
+            if count == self.n:
+                pending.append(dist.all_reduce(self.flat, async_op=True))
+            else:
+                pending.append(dist.all_reduce(self.gf[first:first + count], async_op=True))
+                pending.append(dist.all_reduce(self.gx[first:first + count], async_op=True))
 
         self.ras.end_gradient_batch(chunks if world > 1 else 1, after_chunk if world > 1 else None)
         for work in pending:
@@ -447,7 +458,8 @@ def run_b200(args):
         return ((step * world + rank) * VIEWS_PER_RANK + j) % NUM_VIEWS
 
     def finish_step():
-        rig.finish_step(dist, world)   # per-point backward of the 8 views + the exchange of the N x 59 gradient
+        # per-point backward of the 8 views + the exchange of the N x 59 gradient
+        rig.finish_step(dist, world, args.exchange_chunks)
 
     def resident_view(i):
         def per_view(j, stream):
@@ -601,7 +613,7 @@ def run_b200(args):
     torch.cuda.empty_cache()
     c4 = None
     if not args.no_c4:
-        c4 = run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier)
+        c4 = run_c4_leg(torch, dist, impl, dev, rank, world, max(1, args.c4_lanes), args, barrier)
 
     m, k = int(info["num_points_in_camera"]), int(info["num_keys"])
     if rank != 0:
@@ -699,8 +711,8 @@ def run_b200(args):
                    "near": 0.8, "far": 1000.0, "depth_to_sort_key_scale": 100.0,
                    "visible_points": m, "keys": k, "views": NUM_VIEWS,
                    "step": f"{VIEWS_PER_RANK} views forward+backward per rank as one gradient batch (per-point "
-                           "chain rule of all views in one pass over the points), the N x 59 gradient all-reduced "
-                           "in 8 point ranges that overlap that pass; an iteration (it) = one view forward+backward",
+                           "chain rule of all views in one pass over the points), then one all-reduce of the "
+                           "N x 59 gradient; an iteration (it) = one view forward+backward",
                    "views_per_rank_per_step": VIEWS_PER_RANK,
                    "lanes": lanes, "priority_sections": prio,
                    "lanes_note": f"view j of a step runs on CUDA stream j mod {lanes}; `stages` / `roofline` are "
@@ -762,7 +774,7 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     def step(mine, exchange=True):
         rig.begin_step()
         total = render_views(mine)
-        rig.finish_step(dist, world if exchange else 1)
+        rig.finish_step(dist, world if exchange else 1, args.exchange_chunks)
         return total
 
     def timed(fn, steps):

@@ -1,0 +1,88 @@
+#!/usr/bin/env python
+"""What one rank of the 8-GPU C4 run does between two exchanges, on ONE GPU: a step of 8 of the 64 spread
+views over 2M points (976x544), no exchange.  Sweeps the number of lanes and the order of the views, and
+prints the same views' share of a 64-view step (the no-bubble bound: what the rank's views cost inside a
+long step, where views in flight fill each other's gaps and nothing ramps up or drains).
+
+    python tools/exp_c4_rank_step.py [--steps 6]
+"""
+import argparse
+import json
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--steps", type=int, default=6)
+    ap.add_argument("--views", type=int, default=8)
+    args = ap.parse_args()
+    import torch
+
+    import bench
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    from taichi_3d_gaussian_splatting_b200.distributed import assign_views_lpt, view_cost
+
+    dev = torch.device("cuda:0")
+    torch.cuda.set_device(dev)
+    q_np, t_np = bench.make_views_spread(bench.C4_VIEWS)
+    q_dev, t_dev = torch.from_numpy(q_np).to(dev), torch.from_numpy(t_np).to(dev)
+    out = {}
+
+    def make_step(rig, mine, stats=None):
+        def per_view(j, stream):
+            v = mine[j]
+            loss = rig.render_loss(q_dev[v:v + 1], t_dev[v:v + 1], rig.wt_dev)
+            if stats is not None:
+                info = rig.ras.last_forward_info
+                stats[v] = view_cost(info["num_points_in_camera"], info["num_keys"])
+            return loss
+
+        def step():
+            rig.begin_step()
+            rig.run_views(len(mine), per_view)
+            rig.finish_step(None, 1)
+        return step
+
+    def timed(fn, steps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / steps
+
+    rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", 4)
+    costs = {}
+    make_step(rig, list(range(bench.C4_VIEWS)), costs)()
+    torch.cuda.synchronize()
+    cost_list = [costs[v] for v in range(bench.C4_VIEWS)]
+    mine = assign_views_lpt(cost_list, bench.C4_VIEWS // args.views)[0][0]   # rank 0's share at that world size
+    ms_all = timed(make_step(rig, list(range(bench.C4_VIEWS))), 3)
+    share = sum(cost_list[v] for v in mine) / sum(cost_list)
+    out["ms_64_views_4_lanes"] = ms_all
+    out["rank_views"] = mine
+    out["no_bubble_bound_ms"] = ms_all * share
+    del rig
+    for lanes in (1, 2, 4, 8):
+        rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", lanes)
+        orders = {"lpt_order (largest first)": mine,
+                  "smallest_first": list(reversed(mine)),
+                  "interleaved": mine[0::2] + mine[1::2]}
+        for name, order in orders.items():
+            out[f"lanes={lanes} {name}"] = timed(make_step(rig, order), args.steps)
+        del rig
+    print(json.dumps(out, indent=1))
+
+
+if __name__ == "__main__":
+    main()
