@@ -157,6 +157,60 @@ __device__ __forceinline__ void warp_reduce10(float (&v)[10], int lane)
     v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
 }
 
+// Two entries at once: 20 values in 21 shuffles (against 2 x 12).  The first exchange (xor 16) leaves the
+// lower half-warp with entry A's ten half-sums and the upper one with entry B's; the four remaining
+// levels are those of warp_reduce10 one bit further down (no duplicate level is left).  On return a[0] of
+// lane L holds, of entry (L & 16 ? B : A), the total of value index q = 5 b3 + 3 b2 + 2 b1 + b0 when
+// (b2, b1, b0) is one of 000 001 010 100 101; see reduced_slot_pair().
+__device__ __forceinline__ void warp_reduce10_pair(float (&a)[10], const float (&b)[10], int lane)
+{
+    {
+        const bool up = lane & 16;
+#pragma unroll
+        for (int i = 0; i < 10; ++i) {
+            const float send = up ? a[i] : b[i];
+            const float keep = up ? b[i] : a[i];
+            a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+        }
+    }
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const float send = up ? a[i] : a[i + 5];
+            const float keep = up ? a[i + 5] : a[i];
+            a[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+        }
+    }
+    {
+        const bool up = lane & 4;
+        const float s0 = up ? a[0] : a[3], k0 = up ? a[3] : a[0];
+        const float s1 = up ? a[1] : a[4], k1 = up ? a[4] : a[1];
+        const float s2 = up ? a[2] : 0.0f, k2 = up ? 0.0f : a[2];
+        a[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 4);
+        a[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 4);
+        a[2] = k2 + __shfl_xor_sync(0xffffffffu, s2, 4);
+    }
+    {
+        const bool up = lane & 2;
+        const float s0 = up ? a[0] : a[2], k0 = up ? a[2] : a[0];
+        const float s1 = up ? a[1] : 0.0f, k1 = up ? 0.0f : a[1];
+        a[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 2);
+        a[1] = k1 + __shfl_xor_sync(0xffffffffu, s1, 2);
+    }
+    {
+        const bool up = lane & 1;
+        const float s0 = up ? a[0] : a[1], k0 = up ? a[1] : a[0];
+        a[0] = k0 + __shfl_xor_sync(0xffffffffu, s0, 1);
+    }
+}
+__device__ __forceinline__ int reduced_slot_pair(int lane)
+{
+    const int b3 = (lane >> 3) & 1, b2 = (lane >> 2) & 1, b1 = (lane >> 1) & 1, b0 = lane & 1;
+    if (b1 && (b0 || b2)) return -1;
+    return 5 * b3 + 3 * b2 + 2 * b1 + b0;
+}
+
 // value index held by lane L after warp_reduce10, or -1 for padding / duplicate lanes
 __device__ __forceinline__ int reduced_slot(int lane)
 {
@@ -165,6 +219,59 @@ __device__ __forceinline__ int reduced_slot(int lane)
     if (b2 && (b1 || b3)) return -1;
     return 5 * (lane >> 4) + 3 * b3 + 2 * b2 + b1;
 }
+
+// GS_BWD_STAGING: how a batch of 32 records reaches shared memory (compile-time; 0 is the product).
+//   0  register prefetch: every lane loads its entry's 48 bytes one batch ahead (3 LDG.128) and stores them
+//      (3 STS.128) at the top of the batch
+//   1  bulk-async ring: every lane issues ONE cp.async.bulk of its entry's 48 bytes into the other half of a
+//      2-deep ring, completion on an mbarrier per half (no record registers are carried through the visits)
+#ifndef GS_BWD_STAGING
+#define GS_BWD_STAGING 0
+#endif
+#if GS_BWD_STAGING == 1
+__device__ __forceinline__ void bwd_mbar_init(unsigned long long *bar, unsigned count)
+{
+    const unsigned a = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(a), "r"(count));
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+// every lane arrives once per batch; a lane with an entry announces its 48 bytes and starts the copy
+__device__ __forceinline__ void bwd_bulk_stage(void *dst_smem, const void *src, unsigned long long *bar, bool valid)
+{
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst_smem);
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    if (valid) {
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], 48;" ::"r"(b) : "memory");
+        asm volatile(
+            "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], 48, [%2];" ::"r"(d),
+            "l"(src), "r"(b)
+            : "memory");
+    } else {
+        asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(b) : "memory");
+    }
+}
+__device__ __forceinline__ void bwd_mbar_wait(unsigned long long *bar, unsigned parity)
+{
+    const unsigned b = (unsigned)__cvta_generic_to_shared(bar);
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(b),
+        "r"(parity)
+        : "memory");
+}
+#endif
+
+// GS_BWD_PAIR: 1 = the cross-lane sums of two contributing entries are formed together
+// (warp_reduce10_pair): an entry with hits is held back until the next one of its batch arrives
+#ifndef GS_BWD_PAIR
+#define GS_BWD_PAIR 0
+#endif
 
 // resident warps per SM the kernel is compiled for: 20 (<= 96 registers; the product path, no
 // magnitudes) or 16 when the |duv| magnitudes are accumulated too (they need 8 more registers)
@@ -189,14 +296,33 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
 {
     constexpr int kParts = kTilePixels / (kCells * 32);  // warps per tile = units per tile
     constexpr int kPartsPerColumn = kParts / 2;
+#if GS_BWD_STAGING == 1
+    __shared__ __align__(128) float4 s_ring_all[kParts][2][kBatch * 3];
+    __shared__ __align__(8) unsigned long long s_bar_all[kParts][2];
+#else
     __shared__ float4 s_rec_all[kParts][kBatch * 3];
+#endif
     __shared__ __align__(16) float s_out_all[kParts][kBatch * kGradSlots];
 
     const int lane = threadIdx.x & 31;
+#if GS_BWD_STAGING == 1
+    float4 (*s_ring)[kBatch * 3] = s_ring_all[threadIdx.x >> 5];
+    unsigned long long *s_bar = s_bar_all[threadIdx.x >> 5];
+    if (lane == 0) {
+        bwd_mbar_init(s_bar, 32);
+        bwd_mbar_init(s_bar + 1, 32);
+    }
+    __syncwarp();
+    unsigned parity = 0u;  // bit h: the phase of half h to wait for next
+#else
     float4 *s_rec = s_rec_all[threadIdx.x >> 5];
+#endif
     float *s_out = s_out_all[threadIdx.x >> 5];
     const int tiles_per_row = width / kTile;
     const int my_slot = reduced_slot(lane);
+#if GS_BWD_PAIR
+    const int my_pair_slot = reduced_slot_pair(lane);
+#endif
     // unit = (tile, part).  Persistent launch (work != nullptr): every warp pulls units from the
     // counter until they run out; otherwise one CTA per tile, warp w takes part w.
     for (;;) {
@@ -242,6 +368,17 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
     }
 
     // software pipeline: records of the next batch in registers, payload two batches ahead
+#if GS_BWD_STAGING == 1
+    int g_cur = 0, g_next = 0;
+    int half = 0;
+    if (hi_index > start) {   // warp-uniform
+        const int i = hi_index - 1 - lane;
+        if (i >= start) g_cur = __ldg(payload + i);
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // the half was read / patched by this warp
+        bwd_bulk_stage(&s_ring[0][3 * lane], records + (size_t)3 * g_cur, s_bar, i >= start);
+        if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
+    }
+#else
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
     int g_cur = 0, g_next = 0;
     {
@@ -253,6 +390,7 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
         }
         if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
     }
+#endif
 
     for (int top = hi_index; top > start; top -= kBatch) {
         // ---- stage: lane l holds entry top-1-l (reverse order) ---------------------------------
@@ -276,6 +414,34 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
                 my_mask = live & m;
             }
         }
+#if GS_BWD_STAGING == 1
+        float4 *s_rec = s_ring[half];
+        s_out[kGradSlots * lane + 10] = 0.f;
+        // ---- start the next batch's copies into the other half ------------------------------------
+        {
+            const int i = my_i - kBatch;
+            g_cur = g_next;
+            if (top - kBatch > start) {  // warp-uniform
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                bwd_bulk_stage(&s_ring[half ^ 1][3 * lane], records + (size_t)3 * g_cur, s_bar + (half ^ 1),
+                               i >= start);
+            }
+            if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
+        }
+        // ---- this batch: wait for its 32 copies, then the owner of an entry patches the band constants in
+        bwd_mbar_wait(s_bar + half, (parity >> half) & 1u);
+        parity ^= 1u << half;
+        if (my_i >= start) {
+            float4 q1 = s_rec[3 * lane + 1], q2 = s_rec[3 * lane + 2];
+            const BandConsts band = band_consts(q1.y * q1.z, q2.w);
+            q1.y = band.xlo;   // c xlo opacity red
+            q2.z = band.hi;    // green blue hi s
+            s_rec[3 * lane + 1] = q1;
+            s_rec[3 * lane + 2] = q2;
+        }
+        half ^= 1;
+        __syncwarp();
+#else
         {
             const BandConsts band = band_consts(n1.y * n1.z, n2.w);
             s_rec[3 * lane] = n0;
@@ -294,8 +460,13 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             if (i - kBatch >= start) g_next = __ldg(payload + i - kBatch);
         }
         __syncwarp();
+#endif
 
         unsigned pending = __ballot_sync(0xffffffffu, my_mask != 0u);
+#if GS_BWD_PAIR
+        float held[10];
+        int held_k = -1, held_count = 0;  // warp-uniform
+#endif
         while (pending) {
             const int k = __ffs(pending) - 1;
             pending &= pending - 1u;
@@ -354,10 +525,35 @@ blend_bwd_kernel(int height, int width, const int32_t *__restrict__ tile_start,
             v[3] *= 0.5f;
             v[4] *= 0.5f;
             v[8] *= (1.0f - r1.z);  // dlogit = sum(sa) * (1 - opacity)
+#if GS_BWD_PAIR
+            if (held_k < 0) {  // warp-uniform: wait for a partner
+#pragma unroll
+                for (int q = 0; q < 10; ++q) held[q] = v[q];
+                held_k = k;
+                held_count = count;
+                continue;
+            }
+            warp_reduce10_pair(held, v, lane);
+            {
+                const int kk = (lane & 16) ? k : held_k;
+                if (my_pair_slot >= 0) s_out[kGradSlots * kk + my_pair_slot] = held[0];
+                if (lane == 1) s_out[kGradSlots * held_k + 10] = (float)held_count;
+                if (lane == 17) s_out[kGradSlots * k + 10] = (float)count;
+            }
+            held_k = -1;
+#else
             warp_reduce10(v, lane);
             if (my_slot >= 0) s_out[kGradSlots * k + my_slot] = v[0];
             if (lane == 1) s_out[kGradSlots * k + 10] = (float)count;
+#endif
         }
+#if GS_BWD_PAIR
+        if (held_k >= 0) {  // the batch's odd one out
+            warp_reduce10(held, lane);
+            if (my_slot >= 0) s_out[kGradSlots * held_k + my_slot] = held[0];
+            if (lane == 1) s_out[kGradSlots * held_k + 10] = (float)held_count;
+        }
+#endif
         __syncwarp();
         // ---- flush: lane l owns entry l of the batch ------------------------------------------
         if (my_mask != 0u) {
