@@ -94,7 +94,7 @@ int gs_project_cull_sh(const float *xyz, float *features, const int8_t *invalid_
  * CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE
  * REFERENCE.  Same arguments, meaning and results as
  * gs_project_cull_sh minus `workspace`: the look-back scratch lives in a file-scope device array of the
- * library (8 bytes per 256 points, ~512 KiB; every GPU that loads the library holds it until exit),
+ * library (8 bytes per 128 points, 1 MiB; every GPU that loads the library holds it until exit),
  * whose device address is resolved once per device.  Calls no cudaMalloc / cudaFree / allocating
  * routine.  n > GS_PROJECT_STATIC_MAX_POINTS returns GS_E_STATIC_LIMIT.  All calls on a device share the
  * array; each call clears what it uses first (in stream order), so calls in sequence are independent,

@@ -29,6 +29,18 @@
 
 namespace {
 
+// GS_BIN_TIGHT_LOOPS: 1 (default) = the three short data-dependent loops of a pass (mark, scatter,
+// copy-out: 2 to 4 trips each) are not unrolled: the unrolled forms pay their remainder handling on every
+// entry (C2 0.148 -> 0.142 ms, C5 1.369 -> 1.357 ms for the whole call)
+#ifndef GS_BIN_TIGHT_LOOPS
+#define GS_BIN_TIGHT_LOOPS 1
+#endif
+#if GS_BIN_TIGHT_LOOPS
+#define GS_BIN_SHORT_LOOP _Pragma("unroll 1")
+#else
+#define GS_BIN_SHORT_LOOP
+#endif
+
 constexpr int kBinBlock = 256;
 constexpr int kBinChunk = 1024;               // input entries per CTA
 constexpr int kBinWords = kBinChunk / 32;     // mask words per bin
@@ -184,6 +196,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
 #pragma unroll
     for (int j = 0; j < kBinItems; ++j) {
         uint2 *w = s_pair + (j * (kBinBlock / 32) + warp) * nb;
+        GS_BIN_SHORT_LOOP
         for (int b = lo[j]; b <= hi[j]; ++b) atomicOr(&w[b].y, bit);
     }
     __syncthreads();
@@ -244,6 +257,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
 #pragma unroll
         for (int j = 0; j < kBinItems; ++j) {
             const int word = j * (kBinBlock / 32) + warp;
+            GS_BIN_SHORT_LOOP
             for (int b = lo[j]; b <= hi[j]; ++b) {
                 const uint2 pm = s_pair[word * nb + b];
                 out[pm.x + (uint32_t)__popc(pm.y & lt)] = (OutT)value[j];
@@ -276,6 +290,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
         for (int j = 0; j < kBinItems; ++j) {
             const int word = j * (kBinBlock / 32) + warp;
             const int b1 = min(hi[j], ge - 1);
+            GS_BIN_SHORT_LOOP
             for (int b = max(lo[j], gs); b <= b1; ++b) {
                 const uint2 pm = s_pair[word * nb + b];
                 const uint32_t pos = pm.x + (uint32_t)__popc(pm.y & lt);
@@ -287,6 +302,7 @@ bin_pass_kernel(const int32_t *__restrict__ order, const ushort4 *__restrict__ b
             const OutT *src = s_stage + (s_loc[bb] - first);
             OutT *dst = out + s_base[bb];
             const uint32_t cnt = s_total[bb];
+            GS_BIN_SHORT_LOOP
             for (uint32_t i = lane; i < cnt; i += 32) dst[i] = src[i];
         }
         gs = ge;

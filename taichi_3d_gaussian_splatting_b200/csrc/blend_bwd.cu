@@ -800,12 +800,29 @@ int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t 
     const long long fix_ctas = 4ll * li.sms;
     const char *fe = getenv("GS_BWD_FIXUP");  // 0: timing experiments only (results are then NOT exact)
     const bool fixup = !(fe && atoi(fe) == 0);
+    {
+        // tests only: behave like a persistent launch that died half way (its counter pair left at
+        // arbitrary values, the call reporting an error)
+        const char *te = getenv("GS_TEST_POISON_WORK_COUNTER");
+        if (te && atoi(te) == 1 && work) {
+            GS_CUDA_TRY(cudaMemsetAsync(work, 0x7f, sizeof(GsWorkCounter), st));
+            gs_work_counter_failed(work);
+            return GS_E_INVALID;
+        }
+    }
+    GS_CUDA_TRY(gs_work_counter_arm(work, st));
 #define GS_BWD_LAUNCH(MAG)                                                                              \
     do {                                                                                                \
         blend_bwd_kernel<kCells, MAG><<<grid, kThreads, 0, st>>>(                                       \
             height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,   \
             splat_grads, map_on_image, cell_masks, mask_stride, quarter_flags, fix_list, work, units);  \
-        GS_LAUNCH_CHECK();                                                                              \
+        {                                                                                               \
+            const cudaError_t e__ = cudaGetLastError();                                                 \
+            if (e__ != cudaSuccess) {                                                                   \
+                gs_work_counter_failed(work); /* its pair may be half way: the next launch re-arms it */ \
+                return (int)e__;                                                                        \
+            }                                                                                           \
+        }                                                                                               \
         if (fixup) blend_bwd_fixup_kernel<MAG><<<(unsigned)fix_ctas, 128, 0, st>>>(                     \
             height, width, tile_start, tile_end, payload, rec, image_grad, acc_alpha, last_effective,   \
             splat_grads, map_on_image, fix_list);                                                       \

@@ -5,6 +5,7 @@
 
 #include <atomic>
 #include <map>
+#include <set>
 #include <mutex>
 #include <utility>
 
@@ -212,6 +213,10 @@ __device__ __forceinline__ void gs_st_volatile_u32(uint32_t *p, uint32_t v)
 // stream runs its launches in order and the last warp of a launch resets the pair, so no memset is
 // needed between launches.  nullptr (table full, allocation failed) = the caller launches one CTA per
 // tile instead.
+// A launch that FAILED (the launch call or the call before it returned an error) may not have re-armed
+// its pair: the launcher reports it with gs_work_counter_failed() and the next gs_work_counter_arm()
+// of that pair zeroes it in stream order before the kernel; a pair that was never reported costs the
+// arm call one lock and a lookup in an empty set.
 struct GsWorkCounter {
     unsigned int next, done;
 };
@@ -249,6 +254,35 @@ inline GsWorkCounter *gs_work_counter(cudaStream_t st)
     GsWorkCounter *c = d.base + d.used++;
     table[{dev, st}] = c;
     return c;
+}
+
+inline std::mutex &gs_work_counter_dirty_lock()
+{
+    static std::mutex mu;
+    return mu;
+}
+inline std::set<GsWorkCounter *> &gs_work_counter_dirty_set()
+{
+    static std::set<GsWorkCounter *> dirty;
+    return dirty;
+}
+// the launch that used `c` did not (or may not) run to its end
+inline void gs_work_counter_failed(GsWorkCounter *c)
+{
+    if (!c) return;
+    std::lock_guard<std::mutex> lock(gs_work_counter_dirty_lock());
+    gs_work_counter_dirty_set().insert(c);
+}
+// before a persistent launch on `st`: re-arms a pair a failed launch left behind
+inline cudaError_t gs_work_counter_arm(GsWorkCounter *c, cudaStream_t st)
+{
+    if (!c) return cudaSuccess;
+    {
+        std::lock_guard<std::mutex> lock(gs_work_counter_dirty_lock());
+        std::set<GsWorkCounter *> &dirty = gs_work_counter_dirty_set();
+        if (dirty.empty() || !dirty.erase(c)) return cudaSuccess;
+    }
+    return cudaMemsetAsync(c, 0, sizeof(GsWorkCounter), st);
 }
 
 // next unit of the calling warp (all lanes get it); units >= total mean "done"

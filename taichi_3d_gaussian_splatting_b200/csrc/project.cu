@@ -11,7 +11,13 @@
 
 namespace {
 
-constexpr int kProjBlock = 256;
+// points per CTA.  The staged feature rows (224 B per point) bound the CTAs per SM: 128-point CTAs keep 28
+// warps resident against 24 with 256, and a CTA-wide barrier holds up four warps instead of eight
+// (C2 0.160 -> 0.155 ms, C5 0.541 -> 0.516 ms for pose inverse + projection)
+#ifndef GS_PROJ_BLOCK
+#define GS_PROJ_BLOCK 128
+#endif
+constexpr int kProjBlock = GS_PROJ_BLOCK;
 constexpr unsigned long long kFlagAggregate = 1ull << 62;
 constexpr unsigned long long kFlagPrefix = 2ull << 62;
 constexpr unsigned long long kValueMask = (1ull << 62) - 1;
@@ -491,7 +497,7 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
 // gs_project_cull_sh_static: the same pass with its look-back scratch in a file-scope device array
 // instead of a caller-allocated workspace, for callers that cannot allocate (CUDA graph capture, serving
 // loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
-// Every GPU that loads the library holds the array (~512 KiB) until exit.  The
+// the run's operators.  Every GPU that loads the library holds the array (1 MiB) until exit.  The
 // array's name is a host-side stand-in in host code, not a device address: the launcher takes its
 // address with cudaGetSymbolAddress once per device, with that device current.  All calls on a device
 // share the array: gs_project_cull_sh clears the words a call uses before its kernel (stream-ordered

@@ -902,6 +902,52 @@ def _blend_case_by_hand(seed=0):
                 payload=payload, start=start, end=end, records=records, first_irregular=m_regular + m_edge)
 
 
+def test_persistent_backward_recovers_from_a_launch_that_left_its_work_counter_half_way(monkeypatch):
+    """The persistent backward blend pulls its units from a {next, done} pair that the last warp of a
+    launch re-arms (csrc/gs_common.cuh).  A launch that dies before that leaves the pair at arbitrary
+    values; the launcher records the failure and the next call on that stream zeroes the pair first.
+    GS_TEST_POISON_WORK_COUNTER=1 makes one call behave like such a launch (pair overwritten, error
+    returned): without the re-arm the following call would find next >= units, do nothing and return
+    zeros."""
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+    capi = _lib()
+    lib = capi.lib
+    monkeypatch.setenv("GS_BLEND_PERSISTENT", "1")
+    scene = make_scene(20000, 320, 240, seed=77, scale_factor=0.01)
+    t = util.scene_tensors(scene)
+    cfg = impl.GaussianPointCloudRasterisation.GaussianPointCloudRasterisationConfig()
+    cam = CameraInfo(camera_intrinsics=t["camera_intrinsics"], camera_height=240, camera_width=320, camera_id=0)
+    st = impl._forward_impl(cfg, t["point_cloud"], t["point_cloud_features"], t["point_invalid_mask"],
+                            t["point_object_id"], t["q_pointcloud_camera"], t["t_pointcloud_camera"], cam,
+                            keep_cell_masks=True)
+    g = torch.from_numpy(np.random.default_rng(5).uniform(0, 1, (240, 320, 3)).astype(np.float32)).cuda()
+    scratch = torch.empty(int(lib.gs_blend_bwd_scratch_bytes(240, 320)), dtype=torch.uint8, device="cuda")
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def bwd():
+        grads = torch.zeros(st.m, 12, dtype=torch.float32, device="cuda")
+        status = lib.gs_blend_bwd(240, 320, st.tile_start.data_ptr(), st.tile_end.data_ptr(),
+                                  st.payload.data_ptr(), st.buffers.ptr("records"), g.data_ptr(),
+                                  st.acc_alpha.data_ptr(), st.last.data_ptr(), grads.data_ptr(), None,
+                                  st.cell_masks.data_ptr(), st.k, st.quarter_flags.data_ptr(),
+                                  scratch.data_ptr(), stream)
+        torch.cuda.synchronize()
+        return status, grads
+
+    status, want = bwd()
+    assert status == 0 and float(want.abs().sum()) > 0
+    monkeypatch.setenv("GS_TEST_POISON_WORK_COUNTER", "1")
+    status, nothing = bwd()
+    assert status != 0 and not nothing.any()
+    monkeypatch.delenv("GS_TEST_POISON_WORK_COUNTER")
+    for _ in range(2):   # the call after the failure, and one more (the pair re-arms itself again)
+        status, got = bwd()
+        assert status == 0
+        l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
+        assert l2 <= 1e-6 and mx <= 1e-6, (l2, mx)
+
+
 @pytest.mark.parametrize("magnitude", [True, False])
 @pytest.mark.parametrize("persistent", ["1", "0"])
 def test_blend_backward_decides_like_the_reference_on_irregular_and_edge_entries(
