@@ -788,6 +788,11 @@ int launch_bwd(int tiles, cudaStream_t st, int height, int width, const int32_t 
             GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, true>, kThreads, 0));
         else
             GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, blend_bwd_kernel<kCells, false>, kThreads, 0));
+        // GS_BWD_CTAS_PER_SM: run the persistent grid with fewer CTAs per SM than fit (read once per
+        // device): registers and warp slots left over let another stream's small kernels (projection,
+        // sorts, binning of the next view) run beside this one instead of behind it
+        const char *ce = getenv("GS_BWD_CTAS_PER_SM");
+        if (ce && atoi(ce) > 0 && atoi(ce) < per_sm) per_sm = atoi(ce);
         li.resident = li.sms * (per_sm > 0 ? per_sm : 1);
     }
     GS_CUDA_TRY(cudaMemsetAsync(fix_list, 0, sizeof(unsigned), st));  // the list's counter
