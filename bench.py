@@ -77,6 +77,9 @@ def parse_args():
     ap.add_argument("--priority-sections", type=int, default=0,
                     help="with lanes > 1: the small kernels of a view (projection, sorts, binning, per-point "
                          "backward) run on a high-priority companion stream of the lane")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: the step's exchange -- fused into the per-point pass over NVLink multicast "
+                         "(falls back to nccl if symmetric memory has no multicast mapping), or NCCL's all_reduce")
     ap.add_argument("--exchange-chunks", type=int, default=1,
                     help="N > 1: point ranges the per-point backward of a step is cut into, each all-reduced as "
                          "soon as it is written (1 = one all-reduce after the pass)")
@@ -316,7 +319,7 @@ class Rig:
     """One workload resident on this rank's GPU: the cloud as nn.Parameters, the operator, one flat
     N x 59 gradient buffer the batch extension sums into, and the lane streams."""
 
-    def __init__(self, torch, impl, dev, workload, lanes):
+    def __init__(self, torch, impl, dev, workload, lanes, peer_exchange=False):
         from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
         from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
         self.torch, self.impl, self.dev = torch, impl, dev
@@ -334,7 +337,20 @@ class Rig:
         self.wt_dev = self.wt_host.to(dev)
         self.ras = self.Ras(self.Ras.GaussianPointCloudRasterisationConfig())
         # features first: their rows are added as 16-byte vectors (224 n is a multiple of 16 for every n)
-        self.flat = torch.zeros(n * 59, dtype=torch.float32, device=dev)
+        # N > 1 on NVSwitch: the buffer is symmetric memory and the step ends in the fused pass + exchange
+        # kernel (gs_point_bwd_batch_exchange); otherwise (one GPU, no multicast mapping, --exchange nccl) a
+        # plain buffer, the pass, and NCCL's all_reduce
+        self.peer, self.peer_note = None, "nccl all_reduce after the per-point pass"
+        if peer_exchange:
+            try:
+                from taichi_3d_gaussian_splatting_b200.distributed import PeerExchange
+                self.peer = PeerExchange(n, dev)
+                self.peer_note = ("fused: gs_point_bwd_batch_exchange (ranges reduced in the NVLink switch with "
+                                  f"multimem.ld_reduce / multimem.st while later ranges are computed, "
+                                  f"{self.peer.chunks} ranges)")
+            except Exception as e:  # noqa: BLE001
+                self.peer_note = f"nccl all_reduce (no symmetric-memory multicast: {type(e).__name__}: {str(e)[:120]})"
+        self.flat = self.peer.flat if self.peer is not None else torch.zeros(n * 59, dtype=torch.float32, device=dev)
         self.gf, self.gx = self.flat[:56 * n].view(n, 56), self.flat[56 * n:].view(n, 3)
         self.lanes = max(1, lanes)
         self.lane_streams = [torch.cuda.Stream(dev) for _ in range(self.lanes)] if self.lanes > 1 else []
@@ -350,6 +366,10 @@ class Rig:
         and the all-reduce of a range starts as soon as the range is written (measured, not adopted: at
         N = 8 eight ranges cost 14.17 ms per step against 13.3 with one all-reduce -- sixteen small
         collectives cost more than the 0.3 ms of computation they can hide behind)."""
+        if world > 1 and self.peer is not None:
+            self.ras.end_gradient_batch(exchange=self.peer)
+            self.xyz.grad, self.feat.grad = self.gx, self.gf
+            return
         pending = []
 
         def after_chunk(index, first, count):
@@ -443,7 +463,7 @@ def run_b200(args):
         return float(ms.item())
 
     lanes = max(1, min(args.lanes, VIEWS_PER_RANK))
-    rig = Rig(torch, impl, dev, args.workload, lanes)
+    rig = Rig(torch, impl, dev, args.workload, lanes, peer_exchange=world > 1 and args.exchange == "fused")
     n, w, h = rig.n, rig.w, rig.h
     xyz, feat, ras, flat, gx, gf = rig.xyz, rig.feat, rig.ras, rig.flat, rig.gx, rig.gf
     qs_np, ts_np = make_views(NUM_VIEWS)
@@ -609,6 +629,8 @@ def run_b200(args):
     # release the headline workload before the C4 leg allocates its own
     scene_main = rig.scene
     xyz.grad = feat.grad = None
+    rig_exchange_note = rig.peer_note
+    exchange_error = rig.peer.error() if rig.peer is not None else 0
     del rig, xyz, feat, ras, flat, gx, gf, wt_stage, uploads, finished
     torch.cuda.empty_cache()
     c4 = None
@@ -719,6 +741,8 @@ def run_b200(args):
                                  f"timed in a separate single-stream pass of {stage_steps} steps "
                                  f"({ms_single_stream / stage_steps:.3f} ms per step there)",
                    "key_pipeline": info.get("key_pipeline"),
+                   "exchange": rig_exchange_note if world > 1 else "none (one rank)",
+                   "exchange_error": exchange_error,
                    "parallelism": f"views sharded over {world} rank(s), replicated cloud"
                                   + (", NCCL all-reduce of the Nx59 gradient per step" if world > 1 else ""),
                    "l2": "inputs exceed L2 (236 MB of point data read per step)"},
@@ -756,7 +780,7 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     """BASELINE.json configs[3]: 64 distinct views x 2M Gaussians, the views of a step split over the
     ranks (STRONG scaling: E(G) = T(1, 64 views) / (G T(G, 64 views)))."""
     name = "c4_2m_976x544"
-    rig = Rig(torch, impl, dev, name, lanes)
+    rig = Rig(torch, impl, dev, name, lanes, peer_exchange=world > 1 and args.exchange == "fused")
     q_np, t_np = make_views_spread(C4_VIEWS)
     q_dev, t_dev = torch.from_numpy(q_np).to(dev), torch.from_numpy(t_np).to(dev)
     stats = np.zeros((C4_VIEWS, 2), np.float64)   # per view: M, K of the last recorded pass
@@ -840,6 +864,8 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         "value": C4_VIEWS / (ms_step * 1e-3), "unit": "it/s", "ms_per_step": ms_step,
         "ms_per_step_without_exchange": ms_no_exchange,
         "ms_per_step_round_robin_assignment": ms_round_robin,
+        "exchange": rig.peer_note if world > 1 else "none (one rank)",
+        "exchange_error": rig.peer.error() if rig.peer is not None else 0,
         "exchange_ms_alone": ms_exchange_alone, "exchange_bytes": rig.flat.numel() * 4 if world > 1 else 0,
         "assignment": "longest-processing-time first on K + 3 M of the previous pass",
         "rank_load_max_over_mean": max(loads) / (sum(loads) / world),

@@ -280,6 +280,39 @@ int gs_point_bwd_batch(const float *xyz, const float *features, const int32_t *o
                        float alpha_factor, float color_factor, float high_order_color_factor,
                        float *grad_xyz, float *grad_features, void *stream);
 
+/*
+ * gs_point_bwd_batch over ALL n points, fused with the step's one exchange: the sum of the N x 59
+ * gradient over the ranks of a view-sharded step (not in the reference, which is
+ * single-GPU), done in the switch over NVLink multicast while the pass is still running.  One process
+ * per GPU; every rank calls it once per step with the same n, chunk count and epoch.
+ *   The gradient buffer is symmetric memory of 59 n floats rounded up to a multiple of 4, plus 4: feature
+ *   rows first ([n,56]), then positions ([n,3]); `local_base` is this rank's mapping, `multicast_base` the
+ *   multicast mapping of the same allocation (16-byte aligned).  `flags[r]` is rank r's flag array
+ *   (gs_exchange_flag_words(chunks, world) u32, symmetric, zero before the first call) as mapped into
+ *   THIS process; `scratch` is local device memory of gs_exchange_scratch_bytes(chunks).  `epoch` must be
+ *   > 0 and strictly increasing from call to call on a flag array (nothing is reset between steps).
+ *   chunks <= number of 128-point blocks.  reducer_ctas: CTAs that run the reduction (0 = 64).
+ * On return of the KERNEL (stream order) local_base holds the summed gradient on every rank.  A rank that
+ * waits ~2 s for a peer gives up, records a non-zero word at scratch[1] and finishes without hanging.
+ * How the host gets the mappings is its business (torch.distributed._symmetric_memory in this package).
+ */
+typedef struct gs_exchange_t {
+    void *multicast_base;
+    float *local_base;
+    void *flags[16];
+    int32_t rank, world, chunks, reducer_ctas;
+    uint32_t epoch;
+    uint32_t reserved;
+    void *scratch;
+} gs_exchange_t;
+int64_t gs_exchange_flag_words(int chunks, int world);
+int64_t gs_exchange_scratch_bytes(int chunks);
+int gs_point_bwd_batch_exchange(const float *xyz, const float *features, const int32_t *object_id,
+                                int64_t n, const gs_view_t *views_device, int num_views,
+                                int color_max_sh_band, float q_factor, float s_factor, float alpha_factor,
+                                float color_factor, float high_order_color_factor,
+                                const gs_exchange_t *exchange /* host */, void *stream);
+
 /* ---------------------------------------------------------------------------------------------
  * Loss front-end: what runs between the rasteriser's image and the
  * cotangent handed back to gs_blend_bwd.  Replaces, per iteration, GaussianPointTrainer.py:172-182

@@ -18,7 +18,7 @@ from __future__ import annotations
 import ctypes as C
 import os
 from dataclasses import dataclass
-from typing import Callable, Dict, Optional
+from typing import Any, Callable, Dict, Optional
 
 import torch
 
@@ -335,16 +335,20 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
         self._batch = _GradientBatch(grad_point_cloud, grad_point_cloud_features)
 
     def end_gradient_batch(self, chunks: int = 1,
-                           after_chunk: Optional[Callable[[int, int, int], None]] = None) -> int:
+                           after_chunk: Optional[Callable[[int, int, int], None]] = None,
+                           exchange: Any = None) -> int:
         """Runs the parked views' per-point backward on the current stream (the caller has made it wait
         for the streams the views ran on) and leaves batch mode.  With chunks > 1 the points are cut into
         that many id ranges, one launch each, and `after_chunk(index, first_point, num_points)` is called
         after each launch -- e.g. to start the all-reduce of that range while the next one is computed.
+        exchange: a distributed.PeerExchange whose buffers the batch was begun on -- the pass and the sum of
+        the gradient over the ranks then run as ONE kernel (gs_point_bwd_batch_exchange: ranges are reduced
+        in the NVLink switch while later ranges are computed); every rank must have parked at least one view.
         Returns the number of views that were in the batch."""
         batch, self._batch = self._batch, None
         if batch is None:
             raise RuntimeError("end_gradient_batch without begin_gradient_batch")
-        return batch.finish(self.config, max(1, int(chunks)), after_chunk)
+        return batch.finish(self.config, max(1, int(chunks)), after_chunk, exchange)
 
     def forward(self, input_data: "GaussianPointCloudRasterisation.GaussianPointCloudRasterisationInput"):
         camera_info = input_data.camera_info
@@ -385,10 +389,16 @@ class _GradientBatch:
                                pic=buf.view("point_in_camera", max(st.m, 1)).clone(),
                                sg=splat_grads, K=st.intrinsics, q_cam=st.q_cam, t_pc=t_pc))
 
-    def finish(self, cfg, chunks: int, after_chunk) -> int:
+    def finish(self, cfg, chunks: int, after_chunk, exchange=None) -> int:
         n = self.grad_xyz.shape[0]
         dev = self.grad_xyz.device
         cur = torch.cuda.current_stream(dev)
+        if exchange is not None:
+            if self.common is None:
+                raise _capi.GsError("the fused exchange needs at least one view of the batch on every rank")
+            if (self.grad_features.data_ptr() != exchange.grad_features.data_ptr()
+                    or self.grad_xyz.data_ptr() != exchange.grad_xyz.data_ptr() or exchange.n != n):
+                raise ValueError("the gradient batch was not begun on the exchange's buffers")
         if self.common is None:            # no view on this rank: the gradient is zero
             self.grad_xyz.zero_()
             self.grad_features.zero_()
@@ -404,6 +414,17 @@ class _GradientBatch:
                 t.record_stream(cur)       # produced on the view's lane, consumed here
         table = torch.tensor(rows, dtype=torch.int64).pin_memory().to(dev, non_blocking=True)
         band = self.common[3]
+        if exchange is not None:
+            _capi.check(_lib.gs_point_bwd_batch_exchange(
+                xyz.detach().contiguous().data_ptr(), features.detach().data_ptr(),
+                object_id.contiguous().data_ptr(), n, table.data_ptr(), len(rows), band,
+                float(cfg.grad_q_factor), float(cfg.grad_s_factor), float(cfg.grad_alpha_factor),
+                float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
+                exchange.next_call(), cur.cuda_stream), "gs_point_bwd_batch_exchange")
+            _mark("point_bwd_batch_exchange")
+            num = len(self.views)
+            self.views = []
+            return num
         chunks = max(1, min(chunks, (n + 127) // 128))
         per = ((n + chunks - 1) // chunks + 127) // 128 * 128
         first, index = 0, 0

@@ -14,12 +14,19 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = _build.LIB
 
-ABI_VERSION = 111
+ABI_VERSION = 112
 
 _p = C.c_void_p
 _i = C.c_int
 _l = C.c_int64
 _f = C.c_float
+
+class gs_exchange_t(C.Structure):
+    """include/gs_b200.h: what gs_point_bwd_batch_exchange needs to know about the symmetric buffers."""
+    _fields_ = [("multicast_base", C.c_void_p), ("local_base", C.c_void_p), ("flags", C.c_void_p * 16),
+                ("rank", C.c_int32), ("world", C.c_int32), ("chunks", C.c_int32), ("reducer_ctas", C.c_int32),
+                ("epoch", C.c_uint32), ("reserved", C.c_uint32), ("scratch", C.c_void_p)]
+
 
 # name -> (restype, argtypes); must list every symbol of include/gs_b200.h
 SIGNATURES = {
@@ -41,6 +48,10 @@ SIGNATURES = {
     "gs_project_cull_sh": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
                                 _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "gs_point_bwd_batch": (_i, [_p, _p, _p, _l, _l, _p, _i, _i, _f, _f, _f, _f, _f, _p, _p, _p]),
+    "gs_exchange_flag_words": (_l, [_i, _i]),
+    "gs_exchange_scratch_bytes": (_l, [_i]),
+    "gs_point_bwd_batch_exchange": (_i, [_p, _p, _p, _l, _p, _i, _i, _f, _f, _f, _f, _f,
+                                         C.POINTER(gs_exchange_t), _p]),
     # no workspace argument: its scratch is a file-scope device array of the library (no allocation)
     "gs_project_cull_sh_static": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
                                        _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),

@@ -42,11 +42,13 @@ struct BatchParams {
     float *grad_features;
 };
 
-__global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_kernel(BatchParams p)
+typedef float4 BatchRows[32 * kRowStride4];
+
+// one block of 128 consecutive points (block index `block` of the range), all views
+__device__ __forceinline__ void batch_block(const BatchParams &p, BatchRows *s_rows, const long long block)
 {
-    __shared__ float4 s_rows[kBatchBlock / 32][32 * kRowStride4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const long long local = (long long)blockIdx.x * kBatchBlock + threadIdx.x;
+    const long long local = block * kBatchBlock + threadIdx.x;
     const bool valid = local < p.count;
     const long long pid = p.first + local;
     float4 *rows = s_rows[warp];
@@ -209,7 +211,237 @@ __global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_kernel(BatchParam
     }
 }
 
+__global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_kernel(BatchParams p)
+{
+    __shared__ BatchRows s_rows[kBatchBlock / 32];
+    batch_block(p, s_rows, (long long)blockIdx.x);
+}
+
+// ---- the pass fused with the step's exchange over NVLink / NVSwitch -------------------------------------
+// One launch does the per-point pass AND the sum of the N x 59 gradient over the ranks.  The gradient
+// buffer is SYMMETRIC memory (the same allocation on every rank, mapped into every peer, with a multicast
+// address: a load from it is reduced in the switch over all ranks' copies, a store to it lands in all of
+// them).  The points are cut into `chunks` ranges.  CTAs take one of two roles:
+//   compute CTAs  pull blocks of 128 points by ticket (in order) and write their rows into the LOCAL copy;
+//                 the CTA that completes a range tells every rank so (a flag in that rank's flag array);
+//   reducer CTAs  for each range in turn: wait until every rank has completed it, sum THIS rank's share of
+//                 it over all ranks with multimem.ld_reduce and write the sum to all ranks with multimem.st
+//                 (two-shot all-reduce), then tell every rank; finally wait until every rank has reduced
+//                 every range, so that the buffer is final on this rank when the kernel ends.
+// The reduction of a range thus runs in the switch while the following ranges are computed, with no
+// collective launch per range.  Flags carry the caller's strictly increasing `epoch`, so nothing is reset
+// between steps.  Waits are bounded (~2 s of clock): on expiry the kernel records an error word and goes
+// on instead of hanging the GPU.
+constexpr int kMaxExchangeRanks = 16;
+constexpr long long kSpinLimit = 4000000000ll;
+
+struct ExchangeParams {
+    float *mc_base;      // multicast mapping of the gradient buffer
+    uint32_t *flags[kMaxExchangeRanks];  // every rank's flag array: [2][chunks][world]
+    int rank, world, chunks;
+    uint32_t epoch;
+    uint32_t *scratch;   // local: ticket, error, chunk_done[chunks], reduce_done[chunks]
+    int reducers;        // CTAs in the reducer role
+    long long n;         // points (the buffer holds 56 n feature floats, then 3 n position floats)
+    long long blocks, blocks_per_chunk;
+};
+
+__device__ __forceinline__ void st_release_sys(uint32_t *addr, uint32_t v)
+{
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *addr)
+{
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ float4 multimem_ld_reduce(const float *mc)
+{
+    float4 r;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+                 : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w)
+                 : "l"(mc)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void multimem_st(float *mc, const float4 v)
+{
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "f"(v.x), "f"(v.y),
+                 "f"(v.z), "f"(v.w)
+                 : "memory");
+}
+// wait until *addr >= epoch (flags only grow); false on expiry
+__device__ __forceinline__ bool wait_flag(const uint32_t *addr, uint32_t epoch)
+{
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(addr) - epoch) < 0) {
+        if (clock64() - t0 > kSpinLimit) return false;
+        __nanosleep(64);
+    }
+    return true;
+}
+// this rank's share [lo, hi) of a segment of len4 float4s
+__device__ __forceinline__ void my_share(long long len4, int rank, int world, long long &lo, long long &hi)
+{
+    const long long per = (len4 + world - 1) / world;
+    lo = min(per * rank, len4);
+    hi = min(lo + per, len4);
+}
+
+__global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_exchange_kernel(BatchParams p, ExchangeParams x)
+{
+    __shared__ BatchRows s_rows[kBatchBlock / 32];
+    __shared__ long long s_block;
+    __shared__ bool s_ok;
+    uint32_t *ticket = x.scratch, *error = x.scratch + 1;
+    uint32_t *chunk_done = x.scratch + 2, *reduce_done = x.scratch + 2 + x.chunks;
+    const int tid = threadIdx.x;
+
+    if ((int)blockIdx.x >= x.reducers) {
+        // ---- compute role ----
+        for (;;) {
+            __syncthreads();  // s_block and the staged rows of the previous block are no longer read
+            if (tid == 0) s_block = (long long)atomicAdd(ticket, 1u);
+            __syncthreads();
+            const long long block = s_block;
+            if (block >= x.blocks) return;
+            batch_block(p, s_rows, block);
+            __syncthreads();  // every row of the block has been stored by this CTA
+            if (tid == 0) {
+                __threadfence_system();  // ... and is visible, to the peers too, before the count
+                const int c = (int)(block / x.blocks_per_chunk);
+                const long long in_chunk = min(x.blocks_per_chunk, x.blocks - (long long)c * x.blocks_per_chunk);
+                if (atomicAdd(chunk_done + c, 1u) == (uint32_t)(in_chunk - 1)) {
+                    __threadfence_system();  // the whole range, to every peer, before its flag
+                    for (int r = 0; r < x.world; ++r)
+                        st_release_sys(x.flags[r] + (size_t)c * x.world + x.rank, x.epoch);
+                }
+            }
+        }
+    }
+
+    // ---- reducer role ----
+    const long long threads = (long long)x.reducers * kBatchBlock;
+    const long long me = (long long)blockIdx.x * kBatchBlock + tid;
+    uint32_t *my_flags = x.flags[x.rank];
+    for (int c = 0; c < x.chunks; ++c) {
+        if (tid == 0) s_ok = true;
+        __syncthreads();
+        if (tid < x.world && !wait_flag(my_flags + (size_t)c * x.world + tid, x.epoch)) s_ok = false;
+        __syncthreads();
+        if (!s_ok && tid == 0) atomicExch(error, 1u);
+        // rows [r0, r1) of this range: 56 floats of features each, then 3 floats of positions each
+        const long long r0 = min((long long)c * x.blocks_per_chunk * kBatchBlock, x.n);
+        const long long r1 = min(r0 + x.blocks_per_chunk * kBatchBlock, x.n);
+        const long long seg_base[2] = {14 * r0, 14 * x.n + (3 * r0) / 4};          // in float4s (r0 % 128 == 0)
+        const long long seg_len[2] = {14 * (r1 - r0), (3 * (r1 - r0) + 3) / 4};     // the tail float4 may be padding
+#pragma unroll
+        for (int sgm = 0; sgm < 2; ++sgm) {
+            long long lo, hi;
+            my_share(seg_len[sgm], x.rank, x.world, lo, hi);
+            float4 *mc = reinterpret_cast<float4 *>(x.mc_base) + seg_base[sgm];
+            constexpr int kUnroll = 4;
+            for (long long i = lo + me; i < hi; i += threads * kUnroll) {
+                float4 v[kUnroll];
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    const long long j = i + u * threads;
+                    if (j < hi) v[u] = multimem_ld_reduce(reinterpret_cast<const float *>(mc + j));
+                }
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) {
+                    const long long j = i + u * threads;
+                    if (j < hi) multimem_st(reinterpret_cast<float *>(mc + j), v[u]);
+                }
+            }
+        }
+        __syncthreads();
+        if (tid == 0) {
+            __threadfence_system();
+            if (atomicAdd(reduce_done + c, 1u) == (uint32_t)(x.reducers - 1)) {
+                __threadfence_system();
+                for (int r = 0; r < x.world; ++r)
+                    st_release_sys(x.flags[r] + (size_t)(x.chunks + c) * x.world + x.rank, x.epoch);
+            }
+        }
+    }
+    // the buffer is final here once every rank has reduced its share of every range
+    if (blockIdx.x == 0) {
+        bool ok = true;
+        for (int f = tid; f < x.chunks * x.world; f += kBatchBlock)
+            ok = wait_flag(my_flags + (size_t)x.chunks * x.world + f, x.epoch) && ok;
+        if (!ok) atomicExch(error, 2u);
+    }
+}
+
 }  // namespace
+
+extern "C" int64_t gs_exchange_flag_words(int chunks, int world)
+{
+    return (chunks > 0 && world > 0) ? 2ll * chunks * world : GS_E_INVALID;
+}
+extern "C" int64_t gs_exchange_scratch_bytes(int chunks) { return chunks > 0 ? 4ll * (2 + 2 * chunks) : GS_E_INVALID; }
+
+extern "C" int gs_point_bwd_batch_exchange(const float *xyz, const float *features, const int32_t *object_id,
+                                           int64_t n, const gs_view_t *views_device, int num_views,
+                                           int color_max_sh_band, float q_factor, float s_factor,
+                                           float alpha_factor, float color_factor, float high_order_color_factor,
+                                           const gs_exchange_t *exchange, void *stream)
+{
+    if (n <= 0 || num_views < 0 || !exchange) return GS_E_INVALID;
+    const gs_exchange_t &e = *exchange;
+    if (e.world < 2 || e.world > kMaxExchangeRanks || e.rank < 0 || e.rank >= e.world || e.chunks < 1 ||
+        e.epoch == 0 || !e.multicast_base || !e.local_base || !e.scratch)
+        return GS_E_INVALID;
+    if (!xyz || !features || !object_id || (num_views > 0 && !views_device)) return GS_E_INVALID;
+    if (((uintptr_t)features | (uintptr_t)e.local_base | (uintptr_t)e.multicast_base | (uintptr_t)views_device) & 15u)
+        return GS_E_INVALID;
+    cudaStream_t st = (cudaStream_t)stream;
+    BatchParams p;
+    p.xyz = xyz; p.features = features; p.object_id = object_id;
+    p.first = 0; p.count = n; p.views = views_device; p.num_views = num_views;
+    p.keep = color_max_sh_band <= 0 ? 1 : color_max_sh_band == 1 ? 4 : color_max_sh_band == 2 ? 9 : 16;
+    p.q_factor = q_factor; p.s_factor = s_factor; p.alpha_factor = alpha_factor;
+    p.color_factor = color_factor; p.high_order_color_factor = high_order_color_factor;
+    p.grad_features = e.local_base;                    // features first (16-byte aligned rows for every n)
+    p.grad_xyz = e.local_base + (size_t)GS_FEATURES * n;
+    ExchangeParams x;
+    x.mc_base = (float *)e.multicast_base;
+    for (int r = 0; r < kMaxExchangeRanks; ++r) x.flags[r] = r < e.world ? (uint32_t *)e.flags[r] : nullptr;
+    for (int r = 0; r < e.world; ++r)
+        if (!x.flags[r]) return GS_E_INVALID;
+    x.rank = e.rank; x.world = e.world; x.chunks = e.chunks; x.epoch = e.epoch;
+    x.scratch = (uint32_t *)e.scratch;
+    x.n = n;
+    x.blocks = (n + kBatchBlock - 1) / kBatchBlock;
+    x.blocks_per_chunk = (x.blocks + e.chunks - 1) / e.chunks;
+    // every range must hold at least one block: fewer ranges for a tiny cloud
+    x.chunks = (int)((x.blocks + x.blocks_per_chunk - 1) / x.blocks_per_chunk);
+    static int resident[64];
+    int dev = 0;
+    GS_CUDA_TRY(cudaGetDevice(&dev));
+    if (resident[dev & 63] == 0) {
+        int sms = 0, per_sm = 0;
+        GS_CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        GS_CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, point_bwd_batch_exchange_kernel,
+                                                                  kBatchBlock, 0));
+        resident[dev & 63] = sms * (per_sm > 0 ? per_sm : 1);
+    }
+    int reducers = e.reducer_ctas > 0 ? e.reducer_ctas : 64;
+    if (reducers > resident[dev & 63] / 2) reducers = resident[dev & 63] / 2;
+    if (reducers < 1) reducers = 1;
+    x.reducers = reducers;
+    long long compute = resident[dev & 63] - reducers;
+    if (compute > x.blocks) compute = x.blocks;
+    if (compute < 1) compute = 1;
+    // NOTE: the flag words of a launch use the caller's chunk count for their layout
+    if (x.chunks != e.chunks) return GS_E_INVALID;
+    GS_CUDA_TRY(cudaMemsetAsync(x.scratch, 0, (size_t)gs_exchange_scratch_bytes(x.chunks), st));
+    point_bwd_batch_exchange_kernel<<<(unsigned)(reducers + compute), kBatchBlock, 0, st>>>(p, x);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
 
 extern "C" int gs_point_bwd_batch(const float *xyz, const float *features, const int32_t *object_id,
                                   int64_t first_point, int64_t num_points, const gs_view_t *views_device,

@@ -49,6 +49,71 @@ def assign_views_lpt(costs: Sequence[float], world: int) -> Tuple[List[List[int]
     return mine, loads
 
 
+class PeerExchange:
+    """The buffers of the fused per-point pass + exchange (gs_point_bwd_batch_exchange, include/gs_b200.h):
+    the flat N x 59 gradient as SYMMETRIC memory (one allocation per rank, mapped into every peer, with an
+    NVLink multicast address) and a symmetric flag array, set up with torch.distributed._symmetric_memory
+    (plumbing: allocation and the exchange of the mappings; the reduction itself is this package's kernel).
+    Collective: every rank of `group` constructs it at the same point.  Raises if the devices have no
+    multicast mapping (no NVSwitch, or one GPU): the caller then keeps NCCL's all_reduce.
+
+    grad_features [N,56] / grad_xyz [N,3] are views of `flat` (features first, as everywhere); pass them to
+    begin_gradient_batch and the object to end_gradient_batch(exchange=...)."""
+
+    def __init__(self, n: int, device: torch.device, group: Optional[dist.ProcessGroup] = None,
+                 chunks: int = 16, reducer_ctas: int = 0):
+        import ctypes as C
+
+        import torch.distributed._symmetric_memory as symm_mem
+
+        from . import _capi
+        group = group if group is not None else dist.group.WORLD
+        self.n, self.group = int(n), group
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world < 2 or self.world > 16:
+            raise RuntimeError("the fused exchange is for 2..16 ranks")
+        blocks = (self.n + 127) // 128
+        per = (blocks + max(1, chunks) - 1) // max(1, chunks)
+        self.chunks = (blocks + per - 1) // per           # the library's own rule (every range >= one block)
+        numel = (59 * self.n + 3) // 4 * 4 + 4            # the position segment's last 16-byte vector may overhang
+        self._all = symm_mem.empty(numel, dtype=torch.float32, device=device)
+        self._all.zero_()
+        self._handle = symm_mem.rendezvous(self._all, group.group_name)
+        if not getattr(self._handle, "multicast_ptr", 0):
+            raise RuntimeError("no NVLink multicast mapping for symmetric memory on this system")
+        words = int(_capi.lib.gs_exchange_flag_words(self.chunks, self.world))
+        self._flags = symm_mem.empty(words, dtype=torch.int32, device=device)
+        self._flags.zero_()
+        self._flag_handle = symm_mem.rendezvous(self._flags, group.group_name)
+        self._scratch = torch.zeros(int(_capi.lib.gs_exchange_scratch_bytes(self.chunks)) // 4,
+                                    dtype=torch.int32, device=device)
+        torch.cuda.synchronize(device)
+        dist.barrier(group)                               # every rank's flags are zero before anyone writes
+        self.flat = self._all[:59 * self.n]
+        self.grad_features = self.flat[:56 * self.n].view(self.n, 56)
+        self.grad_xyz = self.flat[56 * self.n:].view(self.n, 3)
+        self.epoch = 0
+        x = _capi.gs_exchange_t()
+        x.multicast_base = int(self._handle.multicast_ptr)
+        x.local_base = self._all.data_ptr()
+        ptrs = list(self._flag_handle.buffer_ptrs)
+        for r in range(self.world):
+            x.flags[r] = int(ptrs[r])
+        x.rank, x.world, x.chunks, x.reducer_ctas = self.rank, self.world, self.chunks, int(reducer_ctas)
+        x.scratch = self._scratch.data_ptr()
+        self._struct, self._byref = x, C.byref(x)
+
+    def next_call(self):
+        """The gs_exchange_t of the next launch (a new epoch: the flags are never reset)."""
+        self.epoch += 1
+        self._struct.epoch = self.epoch
+        return self._byref
+
+    def error(self) -> int:
+        """Non-zero if a launch gave up waiting for a peer (synchronises)."""
+        return int(self._scratch[1].item())
+
+
 @dataclass
 class StepResult:
     loss: torch.Tensor            # sum of the per-view losses over ALL ranks (scalar)
@@ -67,7 +132,8 @@ class ViewShardedTrainerStep:
     def __init__(self, render: Callable[[torch.Tensor, torch.Tensor, Any], torch.Tensor],
                  loss_fn: Callable[[torch.Tensor, Any], torch.Tensor],
                  group: Optional[dist.ProcessGroup] = None, sync_quaternions: bool = True,
-                 rasteriser: Any = None, lanes: int = 4, balance: bool = False, exchange_chunks: int = 1):
+                 rasteriser: Any = None, lanes: int = 4, balance: bool = False, exchange_chunks: int = 1,
+                 peer_exchange: bool = True):
         """rasteriser: the GaussianPointCloudRasterisation module `render` calls, if the step should
         use its fused accumulation (`accumulate_gradients_into`): every view's backward then adds
         into one flat N x 59 buffer (no per-view zero fill, no AccumulateGrad pass) and the exchange
@@ -93,7 +159,11 @@ class ViewShardedTrainerStep:
         that pass is cut into this many point ranges and the all-reduce of a range starts as soon as the
         range is written, so that the exchange overlaps the computation of the following ranges.  The
         default is ONE all-reduce after the pass: on 8 B200s the pass is 0.3 ms and every extra NCCL
-        collective costs more than the part of it that it can hide behind."""
+        collective costs more than the part of it that it can hide behind.
+        peer_exchange: on CUDA devices with an NVLink multicast mapping, gradient batches end in the fused
+        pass + exchange kernel (PeerExchange / gs_point_bwd_batch_exchange) instead of the pass followed by
+        NCCL's all_reduce; falls back to NCCL when the mapping cannot be set up, and for a step in which
+        some rank has no view."""
         self.lanes = max(1, int(lanes))
         self._streams: List[Any] = []
         self.render = render
@@ -103,6 +173,9 @@ class ViewShardedTrainerStep:
         self.rasteriser = rasteriser
         self.balance = bool(balance) and rasteriser is not None
         self.exchange_chunks = max(1, int(exchange_chunks))
+        self.peer_exchange = bool(peer_exchange)
+        self._peer: Optional[PeerExchange] = None
+        self._peer_failed = False
         self._flat: Optional[torch.Tensor] = None
         self._costs: Optional[List[float]] = None   # per view, from the previous call
 
@@ -164,7 +237,15 @@ class ViewShardedTrainerStep:
         if fused:
             n = point_cloud.shape[0]
             if self._flat is None or self._flat.numel() != n * 59 or self._flat.device != point_cloud.device:
-                self._flat = torch.empty(n * 59, dtype=torch.float32, device=point_cloud.device)
+                self._peer = None
+                if (self.peer_exchange and not self._peer_failed and world > 1 and point_cloud.is_cuda
+                        and not getattr(self.rasteriser, "_has_hook", True)):
+                    try:      # collective: every rank takes the same branch (same n, same devices)
+                        self._peer = PeerExchange(n, point_cloud.device, self.group)
+                    except Exception:   # noqa: BLE001 -- no multicast here: NCCL does the exchange
+                        self._peer_failed = True
+                self._flat = (self._peer.flat if self._peer is not None else
+                              torch.empty(n * 59, dtype=torch.float32, device=point_cloud.device))
             # features first: their rows are added as 16-byte vectors and 224 n is a multiple of 16
             # for every n, 12 n is not
             gf, gx = self._flat[:56 * n].view(n, 56), self._flat[56 * n:].view(n, 3)
@@ -196,7 +277,11 @@ class ViewShardedTrainerStep:
         if fused:
             # whatever reached the parameters through autograd (loss terms outside the rasteriser)
             extra_x, extra_f = point_cloud.grad, point_cloud_features.grad
-            if batched:
+            fused_exchange = (batched and self._peer is not None and extra_x is None and extra_f is None
+                              and len(views) >= world)
+            if fused_exchange:
+                self.rasteriser.end_gradient_batch(exchange=self._peer)
+            elif batched:
                 pending = []
 
                 def after_chunk(index, first, count):
