@@ -277,7 +277,7 @@ __device__ __forceinline__ bool wait_flag(const uint32_t *addr, uint32_t epoch)
     const long long t0 = clock64();
     while ((int)(ld_acquire_sys(addr) - epoch) < 0) {
         if (clock64() - t0 > kSpinLimit) return false;
-        __nanosleep(64);
+        __nanosleep(256);  // system-scope loads of one word by every waiting CTA: keep them rare
     }
     return true;
 }
@@ -326,9 +326,11 @@ __global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_exchange_kernel(B
     const long long me = (long long)blockIdx.x * kBatchBlock + tid;
     uint32_t *my_flags = x.flags[x.rank];
     for (int c = 0; c < x.chunks; ++c) {
-        if (tid == 0) s_ok = true;
-        __syncthreads();
-        if (tid < x.world && !wait_flag(my_flags + (size_t)c * x.world + tid, x.epoch)) s_ok = false;
+        if (tid == 0) {  // one poller per CTA
+            bool ok = true;
+            for (int r = 0; r < x.world; ++r) ok = wait_flag(my_flags + (size_t)c * x.world + r, x.epoch) && ok;
+            s_ok = ok;
+        }
         __syncthreads();
         if (!s_ok && tid == 0) atomicExch(error, 1u);
         // rows [r0, r1) of this range: 56 floats of features each, then 3 floats of positions each
@@ -341,7 +343,7 @@ __global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_exchange_kernel(B
             long long lo, hi;
             my_share(seg_len[sgm], x.rank, x.world, lo, hi);
             float4 *mc = reinterpret_cast<float4 *>(x.mc_base) + seg_base[sgm];
-            constexpr int kUnroll = 4;
+            constexpr int kUnroll = 8;
             for (long long i = lo + me; i < hi; i += threads * kUnroll) {
                 float4 v[kUnroll];
 #pragma unroll
@@ -428,7 +430,11 @@ extern "C" int gs_point_bwd_batch_exchange(const float *xyz, const float *featur
                                                                   kBatchBlock, 0));
         resident[dev & 63] = sms * (per_sm > 0 ? per_sm : 1);
     }
-    int reducers = e.reducer_ctas > 0 ? e.reducer_ctas : 64;
+    // measured on B200s at 1M points (tools/exp_peer_exchange.py, pass + exchange after 8 views): more
+    // reducer CTAs than this only add contention in the switch (8 ranks: 16 / 32 / 74 / 148 CTAs -> 0.93 /
+    // 0.83 / 0.88 / 1.01 ms against 1.07 ms for the pass followed by NCCL's all_reduce; 2 ranks: 32 / 48 / 74 /
+    // 148 -> 1.03 / 0.94 / 0.91 / 1.08 ms against 0.90 ms)
+    int reducers = e.reducer_ctas > 0 ? e.reducer_ctas : (e.world <= 2 ? 72 : 32);
     if (reducers > resident[dev & 63] / 2) reducers = resident[dev & 63] / 2;
     if (reducers < 1) reducers = 1;
     x.reducers = reducers;

@@ -61,7 +61,7 @@ class PeerExchange:
     begin_gradient_batch and the object to end_gradient_batch(exchange=...)."""
 
     def __init__(self, n: int, device: torch.device, group: Optional[dist.ProcessGroup] = None,
-                 chunks: int = 16, reducer_ctas: int = 0):
+                 chunks: int = 4, reducer_ctas: int = 0):
         import ctypes as C
 
         import torch.distributed._symmetric_memory as symm_mem

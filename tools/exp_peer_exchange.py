@@ -24,7 +24,7 @@ def main():
     ap.add_argument("--width", type=int, default=976)
     ap.add_argument("--height", type=int, default=544)
     ap.add_argument("--views", type=int, default=8)
-    ap.add_argument("--chunks", type=int, default=16)
+    ap.add_argument("--chunks", type=int, default=4)
     ap.add_argument("--reducers", type=int, default=0)
     ap.add_argument("--iters", type=int, default=10)
     args = ap.parse_args()
@@ -84,6 +84,19 @@ def main():
     step_fused()
     torch.cuda.synchronize()
     got = peer.flat
+    step_nccl()
+    torch.cuda.synchronize()
+    again = flat.clone()
+
+    def rows_off(a, b):
+        a2 = torch.cat([a[:56 * n].view(n, 56), a[56 * n:].view(n, 3)], 1).double()
+        b2 = torch.cat([b[:56 * n].view(n, 56), b[56 * n:].view(n, 3)], 1).double()
+        err = (a2 - b2).norm(dim=1) / (b2.norm(dim=1) + 1e-3 * b2.norm(dim=1).median())
+        return {"rows_over_1e-4": int((err > 1e-4).sum()), "max_row_err": float(err.max()),
+                "worst_row": int(err.argmax())}
+    out["rows_fused_vs_nccl"] = rows_off(got, want)
+    out["rows_nccl_vs_nccl"] = rows_off(again, want)
+    out["rel_l2_nccl_vs_nccl"] = float((again.double() - want.double()).norm() / want.double().norm())
     out["rel_l2"] = float((got.double() - want.double()).norm() / want.double().norm())
     out["finite"] = bool(torch.isfinite(got).all())
     out["exchange_error"] = peer.error()
