@@ -840,7 +840,11 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     ms_exchange_alone = None
     verify = None
     if world > 1:
-        ms_exchange_alone = timed(lambda: dist.all_reduce(rig.flat), 5)
+        # NCCL's all_reduce of a buffer of this size, alone, for comparison (an ordinary allocation: the
+        # symmetric buffer of the fused exchange is not one NCCL runs at speed on)
+        plain = torch.zeros_like(rig.flat) if rig.peer is not None else rig.flat
+        ms_exchange_alone = timed(lambda: dist.all_reduce(plain), 5)
+        del plain
         # on-box check of the exchange: the all-reduced gradient of one step against rank 0 rendering all
         # 64 views by itself into the same kind of buffer (rows differ only by the order of the additions)
         step(mine)
@@ -866,7 +870,7 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         "ms_per_step_round_robin_assignment": ms_round_robin,
         "exchange": rig.peer_note if world > 1 else "none (one rank)",
         "exchange_error": rig.peer.error() if rig.peer is not None else 0,
-        "exchange_ms_alone": ms_exchange_alone, "exchange_bytes": rig.flat.numel() * 4 if world > 1 else 0,
+        "exchange_ms_alone": ms_exchange_alone, "exchange_ms_alone_what": "NCCL all_reduce of an ordinary buffer of this size", "exchange_bytes": rig.flat.numel() * 4 if world > 1 else 0,
         "assignment": "longest-processing-time first on K + 3 M of the previous pass",
         "rank_load_max_over_mean": max(loads) / (sum(loads) / world),
         "rank_load_max_over_mean_round_robin": max(rr_loads) / (sum(rr_loads) / world),
