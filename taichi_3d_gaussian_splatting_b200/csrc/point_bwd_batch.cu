@@ -434,7 +434,8 @@ extern "C" int gs_point_bwd_batch_exchange(const float *xyz, const float *featur
     // reducer CTAs than this only add contention in the switch (8 ranks: 16 / 32 / 74 / 148 CTAs -> 0.93 /
     // 0.83 / 0.88 / 1.01 ms against 1.07 ms for the pass followed by NCCL's all_reduce; 2 ranks: 32 / 48 / 74 /
     // 148 -> 1.03 / 0.94 / 0.91 / 1.08 ms against 0.90 ms)
-    int reducers = e.reducer_ctas > 0 ? e.reducer_ctas : (e.world <= 2 ? 72 : 32);
+    // (4 ranks: 48 / 64 -> 0.85 / 0.89 ms against 1.02 ms)
+    int reducers = e.reducer_ctas > 0 ? e.reducer_ctas : (e.world <= 2 ? 72 : e.world <= 4 ? 48 : 32);
     if (reducers > resident[dev & 63] / 2) reducers = resident[dev & 63] / 2;
     if (reducers < 1) reducers = 1;
     x.reducers = reducers;

@@ -92,3 +92,73 @@ def test_fused_pass_and_exchange_equals_pass_then_all_reduce(n):
         # the two paths differ by the order of fp32 additions only (atomics inside a view, ranks in the switch)
         assert status == "ok" and worst <= 1e-5, (rank, worst)
         assert 1 <= chunks <= 4
+
+
+def _step_worker(rank, world, port, out):
+    """ViewShardedTrainerStep on two ranks: the fused pass + exchange against NCCL's all_reduce after the pass
+    (peer_exchange=False), LPT assignment on, six views."""
+    import torch.distributed as dist
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", device_id=dev)
+    try:
+        import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+        from taichi_3d_gaussian_splatting_b200.Camera import CameraInfo
+        from taichi_3d_gaussian_splatting_b200.distributed import ViewShardedTrainerStep
+        from taichi_3d_gaussian_splatting_b200.synthetic import make_scene
+        Ras = impl.GaussianPointCloudRasterisation
+        n, w, h = 20_000, 256, 160
+        scene = make_scene(n, w, h, seed=23, scale_factor=0.02)
+        t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).to(dev)
+        cam = CameraInfo(t(scene.camera_intrinsics), h, w, 0)
+        oid, inv = t(scene.point_object_id), t(scene.point_invalid_mask)
+        q_pc, t_pc = t(scene.q_pointcloud_camera), t(scene.t_pointcloud_camera)
+        g = t(np.random.default_rng(4).uniform(0, 1, (h, w, 3)).astype(np.float32))
+        views = [(0.01 * i, -0.005 * i) for i in range(6)]
+        results = {}
+        for peer_exchange in (False, True):
+            ras = Ras(Ras.GaussianPointCloudRasterisationConfig())
+            xyz = t(scene.point_cloud).requires_grad_(True)
+            feat = t(scene.point_cloud_features).requires_grad_(True)
+
+            def render(p, f, view, ras=ras):
+                image, _, _ = ras(Ras.GaussianPointCloudRasterisationInput(
+                    point_cloud=p, point_cloud_features=f, point_object_id=oid, point_invalid_mask=inv,
+                    camera_info=cam, q_pointcloud_camera=q_pc,
+                    t_pointcloud_camera=t_pc + torch.tensor([[view[0], view[1], 0.0]], device=dev),
+                    color_max_sh_band=3))
+                return image
+
+            step = ViewShardedTrainerStep(render, lambda image, view: (image * g).sum(), rasteriser=ras,
+                                          lanes=2, balance=True, peer_exchange=peer_exchange)
+            for _ in range(3):   # the second call uses the measured costs (LPT), the third a later epoch
+                res = step(xyz, feat, views)
+            torch.cuda.synchronize()
+            results[peer_exchange] = (xyz.grad.clone(), feat.grad.clone(), float(res.loss),
+                                      step._peer is not None)
+        gx0, gf0, loss0, used0 = results[False]
+        gx1, gf1, loss1, used1 = results[True]
+        assert not used0
+        rel_f = float((gf1.double() - gf0.double()).norm() / gf0.double().norm())
+        rel_x = float((gx1.double() - gx0.double()).norm() / gx0.double().norm())
+        out[rank] = (used1, rel_f, rel_x, abs(loss1 - loss0) / abs(loss0))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_view_sharded_step_with_the_fused_exchange_equals_the_nccl_step():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs on one box")
+    import torch.multiprocessing as mp
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    out = mp.Manager().dict()
+    mp.spawn(_step_worker, args=(2, port, out), nprocs=2, join=True)
+    assert set(out.keys()) == {0, 1}
+    if not out[0][0]:
+        pytest.skip("no symmetric-memory multicast here: the step kept NCCL")
+    for rank in (0, 1):
+        used, rel_f, rel_x, rel_loss = out[rank]
+        assert used and rel_f <= 1e-5 and rel_x <= 1e-5 and rel_loss <= 1e-5, out[rank]
