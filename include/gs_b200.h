@@ -294,7 +294,7 @@ int gs_point_bwd_batch(const float *xyz, const float *features, const int32_t *o
  *   chunks <= number of 128-point blocks (4 measured best).  reducer_ctas: CTAs that run the reduction
  *   (0 = the measured optimum: 72 for 2 ranks, 48 up to 4, 32 beyond).
  * On return of the KERNEL (stream order) local_base holds the summed gradient on every rank.  A rank that
- * waits ~2 s for a peer gives up, records a non-zero word at scratch[1] and finishes without hanging.
+ * waits ~10 s for a peer gives up, records a non-zero word at scratch[1] and finishes without hanging.
  * How the host gets the mappings is its business (torch.distributed._symmetric_memory in this package).
  */
 typedef struct gs_exchange_t {

@@ -384,9 +384,10 @@ class _GradientBatch:
         elif common != self.common:
             raise ValueError("the views of a gradient batch must share the point tensors and the colour band")
         buf = st.buffers
-        # small copies, so that the view's large forward buffers can be released now
-        self.views.append(dict(slot=buf.view("slot_of_point", st.n).clone(),
-                               pic=buf.view("point_in_camera", max(st.m, 1)).clone(),
+        # views of the forward's per-point buffer (80 B per point of capacity stay alive until the step's
+        # pass; copying the two arrays out cost 0.02 ms per view at 1M points)
+        self.views.append(dict(slot=buf.view("slot_of_point", st.n),
+                               pic=buf.view("point_in_camera", max(st.m, 1)),
                                sg=splat_grads, K=st.intrinsics, q_cam=st.q_cam, t_pc=t_pc))
 
     def finish(self, cfg, chunks: int, after_chunk, exchange=None) -> int:

@@ -230,10 +230,10 @@ __global__ void __launch_bounds__(kBatchBlock) point_bwd_batch_kernel(BatchParam
 //                 every range, so that the buffer is final on this rank when the kernel ends.
 // The reduction of a range thus runs in the switch while the following ranges are computed, with no
 // collective launch per range.  Flags carry the caller's strictly increasing `epoch`, so nothing is reset
-// between steps.  Waits are bounded (~2 s of clock): on expiry the kernel records an error word and goes
+// between steps.  Waits are bounded (~10 s of clock): on expiry the kernel records an error word and goes
 // on instead of hanging the GPU.
 constexpr int kMaxExchangeRanks = 16;
-constexpr long long kSpinLimit = 4000000000ll;
+constexpr long long kSpinLimit = 20000000000ll;  // ~10 s at 1.9 GHz
 
 struct ExchangeParams {
     float *mc_base;      // multicast mapping of the gradient buffer
