@@ -475,6 +475,8 @@ FULL_SIZE_CASES = {
     # rows could be given here to bound the oracle's time: the cotangent is then zero outside it, so the
     # pairs outside contribute exact zeros; the whole 4K frame takes the oracle ~25 s on 16 cores)
     "c5": ("c5_5m_3840x2160", (0.8, 1000.0, 100.0), None),
+    # BASELINE config 4's cloud and frame (2M points at 976x544), one view of it
+    "c4": ("c4_2m_976x544", (0.8, 1000.0, 100.0), None),
 }
 
 
