@@ -53,7 +53,7 @@ WORKLOADS = {
 }
 METRIC = "fwd+bwd iters/s"  # BASELINE.json metric, first half; the render half rides along (render_*)
 NUM_VIEWS = 8
-VIEWS_PER_RANK = 8   # views each rank renders per step of the headline leg; weak scaling
+VIEWS_PER_RANK = int(os.environ.get("GS_BENCH_VIEWS_PER_STEP", "8"))   # views each rank renders per step of the headline leg (weak scaling; the env override is for experiments)
 C4_VIEWS = 64        # BASELINE.json configs[3]: 64 camera views per step, split over the ranks
 FP32_PEAK_TFLOPS = 148 * 128 * 2 * 1.965e9 / 1e12  # 74.5 (theoretical: 148 SMs x 128 lanes x FMA at 1965 MHz)
 FLOP_PER_PAIR_FWD, FLOP_PER_PAIR_BWD = 28.0, 64.0     # SURVEY.md section 8(d) convention

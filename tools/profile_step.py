@@ -23,6 +23,9 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--workload", default="c2_1m_1920x1088", choices=list(bench.WORKLOADS))
+    ap.add_argument("--batch", type=int, default=0,
+                    help="after the single-view steps, one gradient batch of this many views (the step's "
+                         "per-point pass: point_bwd_batch_kernel)")
     args = ap.parse_args()
     n, w, h, sf, seed = bench.WORKLOADS[args.workload]
     dev = torch.device("cuda:0")
@@ -42,6 +45,18 @@ def main():
             point_cloud=xyz, point_cloud_features=feat, point_object_id=oid, point_invalid_mask=inv,
             camera_info=cam, q_pointcloud_camera=q, t_pointcloud_camera=t, color_max_sh_band=3))
         (image * wt).sum().backward()
+    if args.batch > 0:
+        gf = torch.empty(n, 56, device=dev)
+        gx = torch.empty(n, 3, device=dev)
+        qs, ts = bench.make_views(args.batch)
+        ras.begin_gradient_batch(gx, gf)
+        for v in range(args.batch):
+            image, _, _ = ras(Ras.GaussianPointCloudRasterisationInput(
+                point_cloud=xyz, point_cloud_features=feat, point_object_id=oid, point_invalid_mask=inv,
+                camera_info=cam, q_pointcloud_camera=torch.from_numpy(qs[v:v + 1]).to(dev),
+                t_pointcloud_camera=torch.from_numpy(ts[v:v + 1]).to(dev), color_max_sh_band=3))
+            (image * wt).sum().backward()
+        ras.end_gradient_batch()
     torch.cuda.synchronize()
     print("ok", ras.last_forward_info)
 
