@@ -42,7 +42,10 @@ namespace {
 #endif
 
 constexpr int kBinBlock = 256;
-constexpr int kBinChunk = 1024;               // input entries per CTA
+#ifndef GS_BIN_CHUNK
+#define GS_BIN_CHUNK 1024
+#endif
+constexpr int kBinChunk = GS_BIN_CHUNK;       // input entries per CTA (tuning switch; 2048 measured)
 constexpr int kBinWords = kBinChunk / 32;     // mask words per bin
 constexpr int kBinItems = kBinChunk / kBinBlock;
 constexpr int kMaxBins = 256;                 // tile columns / rows: images up to 4096 x 4096
