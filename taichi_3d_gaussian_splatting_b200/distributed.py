@@ -176,6 +176,7 @@ class ViewShardedTrainerStep:
         self.peer_exchange = bool(peer_exchange)
         self._peer: Optional[PeerExchange] = None
         self._peer_failed = False
+        self._drop_peer = False
         self._flat: Optional[torch.Tensor] = None
         self._costs: Optional[List[float]] = None   # per view, from the previous call
 
@@ -236,6 +237,8 @@ class ViewShardedTrainerStep:
         batched = False
         if fused:
             n = point_cloud.shape[0]
+            if self._drop_peer:
+                self._peer, self._peer_failed, self._flat, self._drop_peer = None, True, None, False
             if self._flat is None or self._flat.numel() != n * 59 or self._flat.device != point_cloud.device:
                 self._peer = None
                 if (self.peer_exchange and not self._peer_failed and world > 1 and point_cloud.is_cuda
@@ -282,6 +285,11 @@ class ViewShardedTrainerStep:
             if fused_exchange:
                 self.rasteriser.end_gradient_batch(exchange=self._peer)
             elif batched:
+                if self._peer is not None and (extra_x is not None or extra_f is not None):
+                    # this training loop sends gradients around the rasteriser every step (the same on every
+                    # rank: they come from the loss configuration): the fused exchange will never apply, and
+                    # NCCL is slow on the symmetric allocation -- from the next step on, a plain buffer
+                    self._drop_peer = True
                 pending = []
 
                 def after_chunk(index, first, count):
