@@ -842,7 +842,8 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     if world > 1:
         # NCCL's all_reduce of a buffer of this size, alone, for comparison (an ordinary allocation: the
         # symmetric buffer of the fused exchange is not one NCCL runs at speed on)
-        plain = torch.zeros_like(rig.flat) if rig.peer is not None else rig.flat
+        plain = (torch.zeros(rig.flat.numel(), dtype=torch.float32, device=dev) if rig.peer is not None
+                 else rig.flat)
         ms_exchange_alone = timed(lambda: dist.all_reduce(plain), 5)
         del plain
         # on-box check of the exchange: the all-reduced gradient of one step against rank 0 rendering all

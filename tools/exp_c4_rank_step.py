@@ -73,7 +73,45 @@ def main():
     out["rank_views"] = mine
     out["no_bubble_bound_ms"] = ms_all * share
     del rig
-    for lanes in (1, 2, 4, 8):
+    # per-view time, alone on one stream (CUDA events around forward + backward of the view)
+    rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", 1)
+    view_ms = []
+    for v in range(bench.C4_VIEWS):
+        ts = []
+        for rep in range(3):
+            rig.begin_step()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rig.render_loss(q_dev[v:v + 1], t_dev[v:v + 1], rig.wt_dev)
+            e1.record()
+            rig.finish_step(None, 1)
+            torch.cuda.synchronize()
+            ts.append(e0.elapsed_time(e1))
+        view_ms.append(min(ts[1:]))
+    del rig
+    world = bench.C4_VIEWS // args.views
+    assignments = {
+        "round_robin": [list(range(r, bench.C4_VIEWS, world)) for r in range(world)],
+        "lpt_on_K+3M": assign_views_lpt(cost_list, world)[0],
+        "lpt_on_measured_ms": assign_views_lpt(view_ms, world)[0],
+    }
+    rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", 8)
+    corr = float(np.corrcoef(np.array(cost_list), np.array(view_ms))[0, 1])
+    out["view_ms_min_max"] = [min(view_ms), max(view_ms)]
+    out["corr_model_vs_measured"] = corr
+    for name, shares in assignments.items():
+        times = [timed(make_step(rig, share), 4) for share in shares]
+        out[f"shares {name}"] = {"max_ms": max(times), "mean_ms": sum(times) / len(times),
+                                 "per_rank_ms": [round(x, 2) for x in times]}
+    del rig
+    for prio in ():   # (measured: no effect, 51.6 against 51.2 ms for 64 views)
+        impl.PRIORITY_SECTIONS = prio
+        rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", 8)
+        out[f"lanes=8 priority_sections={prio} rank share"] = timed(make_step(rig, mine), args.steps)
+        out[f"lanes=8 priority_sections={prio} 64 views"] = timed(make_step(rig, list(range(bench.C4_VIEWS))), 3)
+        del rig
+    impl.PRIORITY_SECTIONS = False
+    for lanes in ():
         rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", lanes)
         orders = {"lpt_order (largest first)": mine,
                   "smallest_first": list(reversed(mine)),
