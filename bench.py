@@ -836,6 +836,8 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         step(mine)
     ms_step = timed(lambda: step(mine), steps)
     ms_no_exchange = timed(lambda: step(mine, exchange=False), steps)
+    if world > 1:
+        step(round_robin[rank])   # other views per rank, other buffer sizes: let the allocator settle first
     ms_round_robin = timed(lambda: step(round_robin[rank]), steps) if world > 1 else ms_step
     ms_exchange_alone = None
     verify = None
