@@ -655,7 +655,10 @@ __device__ __forceinline__ void fixup_pixel(const int lane, const bool replay, c
     bool stopped = false;  // warp-uniform: the replay has passed the hot kernel's last pair of this pixel
     lit.T_carry = fast.T_carry = T_end;
     lit.w_carry = fast.w_carry = 0.0f;
-    int g_next = 0;
+    // software pipeline as in the hot kernel: records one step ahead, payload two steps ahead, so that a
+    // step waits for ONE load latency, not for the dependent payload -> record pair (the pass is a chain of
+    // such steps along the longest flagged pixel's list)
+    int g_next = 0, g_next2 = 0;
     float4 n0 = make_float4(0.f, 0.f, 0.f, 0.f), n1 = n0, n2 = n0;
     {
         const int i = last - 1 - lane;
@@ -664,6 +667,7 @@ __device__ __forceinline__ void fixup_pixel(const int lane, const bool replay, c
             const float4 *src = records + (size_t)3 * g_next;
             n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
         }
+        if (i - kBatch >= start) g_next2 = __ldg(payload + i - kBatch);
     }
     for (int top = last; top > start; top -= kBatch) {
         const int i = top - 1 - lane;
@@ -671,11 +675,12 @@ __device__ __forceinline__ void fixup_pixel(const int lane, const bool replay, c
         const float4 r0 = n0, r1 = n1, r2 = n2;
         {
             const int in = i - kBatch;
+            g_next = g_next2;
             if (in >= start) {
-                g_next = __ldg(payload + in);
                 const float4 *src = records + (size_t)3 * g_next;
                 n0 = __ldg(src); n1 = __ldg(src + 1); n2 = __ldg(src + 2);
             }
+            if (in - kBatch >= start) g_next2 = __ldg(payload + in - kBatch);
         }
         const bool valid = i >= start;
         const float dx = fx - r0.x, dy = fy - r0.y;
