@@ -281,6 +281,17 @@ int gs_point_bwd_batch(const float *xyz, const float *features, const int32_t *o
                        float *grad_xyz, float *grad_features, void *stream);
 
 /*
+ * gs_point_bwd_batch for ONE view over all n points, the view's record passed from the HOST (it travels as
+ * a kernel argument: no device table).  Replaces, for a plain backward without a hook, the zero fill of the
+ * N x 3 / N x 56 gradient tensors (R.py:1051-1058) + gs_point_bwd: every row is stored once, zeros for the
+ * points the view does not see.
+ */
+int gs_point_bwd_all_points(const float *xyz, const float *features, const int32_t *object_id, int64_t n,
+                            const gs_view_t *view /* host */, int color_max_sh_band, float q_factor,
+                            float s_factor, float alpha_factor, float color_factor,
+                            float high_order_color_factor, float *grad_xyz, float *grad_features, void *stream);
+
+/*
  * gs_point_bwd_batch over ALL n points, fused with the step's one exchange: the sum of the N x 59
  * gradient over the ranks of a view-sharded step (not in the reference, which is
  * single-GPU), done in the switch over NVLink multicast while the pass is still running.  One process

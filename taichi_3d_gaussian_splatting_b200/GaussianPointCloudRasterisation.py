@@ -51,6 +51,11 @@ KEY_PIPELINE = os.environ.get("GS_KEY_PIPELINE", "binned")
 # unchanged callers really ran THIS code)
 CALL_COUNTS = {"forward": 0, "backward": 0, "hook": 0}
 
+# A plain backward (no hook, no accumulation target, no batch) stores the gradient rows of all points with
+# gs_point_bwd_all_points instead of zero-filling N x 59 floats and scattering the visible rows into them.
+# GS_STORE_ALL_ROWS=0 keeps the two-step form (tests compare the two).
+STORE_ALL_ROWS = os.environ.get("GS_STORE_ALL_ROWS", "1") != "0"
+
 # set to a profiling.StageProfiler to get one CUDA event per stage (bench.py); None = no events
 STAGE_PROFILER = None
 
@@ -260,7 +265,12 @@ class GaussianPointCloudRasterisation(torch.nn.Module):
                                     camera_info,
                                     keep_cell_masks=ctx.needs_input_grad[0] or ctx.needs_input_grad[1],
                                     hook_outputs=backward_valid_point_hook is not None,
-                                    slots_output=outer._batch is not None)
+                                    # a plain backward without a hook stores the gradient rows of ALL
+                                    # points in one pass (no zero fill): it needs the slot map too
+                                    slots_output=outer._batch is not None or (
+                                        STORE_ALL_ROWS and backward_valid_point_hook is None
+                                        and outer._accumulate_into is None
+                                        and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1])))
                 outer.last_forward_info = out.info
                 ctx.set_materialize_grads(False)
                 ctx.camera_info = camera_info
@@ -710,6 +720,7 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
                    t_pointcloud_camera, camera_info, color_max_sh_band, grad_rasterized_image,
                    hook, hook_input_type, accumulate_into=None, batch=None):
     CALL_COUNTS["backward"] += 1
+    store_all = False
     dev = pointcloud.device
     n, m, W, H = st.n, st.m, st.width, st.height
     s_big = torch.cuda.current_stream(dev)
@@ -722,6 +733,13 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
         grad_pointcloud, grad_features = accumulate_into
         if grad_pointcloud.shape[0] != n or grad_features.shape[0] != n:
             raise ValueError("accumulation buffers do not match the point cloud")
+    elif (STORE_ALL_ROWS and hook is None and m > 0 and st.buffers.has("slot_of_point")
+          and pointcloud_features.data_ptr() % 16 == 0):
+        # plain backward (what the unchanged trainer runs): every row is stored by gs_point_bwd_all_points,
+        # zeros for the points this view does not see -- no zero fill of the N x 59 floats (R.py:1051-1058)
+        store_all = True
+        grad_pointcloud = torch.empty_like(pointcloud, memory_format=torch.contiguous_format)
+        grad_features = torch.empty_like(pointcloud_features, memory_format=torch.contiguous_format)
     else:
         grad_pointcloud = torch.zeros_like(pointcloud)
         grad_features = torch.zeros_like(pointcloud_features, memory_format=torch.contiguous_format)
@@ -756,7 +774,21 @@ def _backward_impl(cfg, st: _ForwardState, pointcloud, pointcloud_features, poin
     h_mag = torch.empty(m, dtype=torch.float32, device=dev) if want_hook else None
     h_aff = torch.empty(m, dtype=torch.int32, device=dev) if want_hook else None
     t_pc = t_pointcloud_camera.detach().to(device=dev, dtype=torch.float32).contiguous()
-    if m > 0:
+    if store_all:
+        view = _capi.gs_view_t()
+        view.slot_of_point, view.point_in_camera = buf.ptr("slot_of_point"), buf.ptr("point_in_camera")
+        view.splat_grads, view.intrinsics = splat_grads.data_ptr(), st.intrinsics.data_ptr()
+        view.q_cam_pc, view.t_pc_cam = st.q_cam.data_ptr(), t_pc.data_ptr()
+        _hand_over(s_big, s_small)
+        import ctypes as _C
+        _capi.check(_lib.gs_point_bwd_all_points(
+            pointcloud.detach().contiguous().data_ptr(), pointcloud_features.detach().data_ptr(),
+            point_object_id.contiguous().data_ptr(), n, _C.byref(view), int(color_max_sh_band),
+            float(cfg.grad_q_factor), float(cfg.grad_s_factor), float(cfg.grad_alpha_factor),
+            float(cfg.grad_color_factor), float(cfg.grad_high_order_color_factor),
+            grad_pointcloud.data_ptr(), grad_features.data_ptr(), s_small.cuda_stream), "gs_point_bwd_all_points")
+        _hand_over(s_small, s_big)
+    elif m > 0:
         _hand_over(s_big, s_small)
         stream = s_small.cuda_stream
         _capi.check(_lib.gs_point_bwd(

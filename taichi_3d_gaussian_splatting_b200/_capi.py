@@ -14,12 +14,19 @@ from . import build as _build
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = _build.LIB
 
-ABI_VERSION = 112
+ABI_VERSION = 113
 
 _p = C.c_void_p
 _i = C.c_int
 _l = C.c_int64
 _f = C.c_float
+
+class gs_view_t(C.Structure):
+    """include/gs_b200.h: one view of a gradient batch (device pointers into its forward / backward state)."""
+    _fields_ = [("slot_of_point", C.c_void_p), ("point_in_camera", C.c_void_p), ("splat_grads", C.c_void_p),
+                ("intrinsics", C.c_void_p), ("q_cam_pc", C.c_void_p), ("t_pc_cam", C.c_void_p),
+                ("reserved", C.c_int64 * 2)]
+
 
 class gs_exchange_t(C.Structure):
     """include/gs_b200.h: what gs_point_bwd_batch_exchange needs to know about the symmetric buffers."""
@@ -48,6 +55,7 @@ SIGNATURES = {
     "gs_project_cull_sh": (_i, [_p, _p, _p, _p, _l, _p, _p, _p, _i, _f, _f, _i, _i, _f,
                                 _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "gs_point_bwd_batch": (_i, [_p, _p, _p, _l, _l, _p, _i, _i, _f, _f, _f, _f, _f, _p, _p, _p]),
+    "gs_point_bwd_all_points": (_i, [_p, _p, _p, _l, C.POINTER(gs_view_t), _i, _f, _f, _f, _f, _f, _p, _p, _p]),
     "gs_exchange_flag_words": (_l, [_i, _i]),
     "gs_exchange_scratch_bytes": (_l, [_i]),
     "gs_point_bwd_batch_exchange": (_i, [_p, _p, _p, _l, _p, _i, _i, _f, _f, _f, _f, _f,

@@ -1,7 +1,7 @@
 // capi.cu -- ABI identification and status strings of libgs_b200.so (see include/gs_b200.h).
 #include "gs_common.cuh"
 
-extern "C" int gs_abi_version(void) { return 112; }
+extern "C" int gs_abi_version(void) { return 113; }
 
 extern "C" const char *gs_status_string(int status)
 {

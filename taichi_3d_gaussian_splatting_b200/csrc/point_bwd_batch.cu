@@ -40,6 +40,8 @@ struct BatchParams {
     float q_factor, s_factor, alpha_factor, color_factor, high_order_color_factor;
     float *grad_xyz;
     float *grad_features;
+    gs_view_t one;      // inline_one != 0: the batch is this one view (no device table)
+    int inline_one;
 };
 
 typedef float4 BatchRows[32 * kRowStride4];
@@ -85,7 +87,7 @@ __device__ __forceinline__ void batch_block(const BatchParams &p, BatchRows *s_r
     float4 *row = rows + lane * kRowStride4;
 
     for (int v = 0; v < p.num_views; ++v) {
-        const gs_view_t &view = p.views[v];
+        const gs_view_t &view = p.inline_one ? p.one : p.views[v];
         const int slot = valid ? __ldg(view.slot_of_point + pid) : -1;
         if (slot < 0) continue;
         const float4 *sg4 = reinterpret_cast<const float4 *>(view.splat_grads + (size_t)kGradSlots * slot);
@@ -406,6 +408,7 @@ extern "C" int gs_point_bwd_batch_exchange(const float *xyz, const float *featur
     p.keep = color_max_sh_band <= 0 ? 1 : color_max_sh_band == 1 ? 4 : color_max_sh_band == 2 ? 9 : 16;
     p.q_factor = q_factor; p.s_factor = s_factor; p.alpha_factor = alpha_factor;
     p.color_factor = color_factor; p.high_order_color_factor = high_order_color_factor;
+    p.inline_one = 0;
     p.grad_features = e.local_base;                    // features first (16-byte aligned rows for every n)
     p.grad_xyz = e.local_base + (size_t)GS_FEATURES * n;
     ExchangeParams x;
@@ -468,7 +471,36 @@ extern "C" int gs_point_bwd_batch(const float *xyz, const float *features, const
     p.q_factor = q_factor; p.s_factor = s_factor; p.alpha_factor = alpha_factor;
     p.color_factor = color_factor; p.high_order_color_factor = high_order_color_factor;
     p.grad_xyz = grad_xyz; p.grad_features = grad_features;
+    p.inline_one = 0;
     const long long blocks = (num_points + kBatchBlock - 1) / kBatchBlock;
+    point_bwd_batch_kernel<<<(unsigned)blocks, kBatchBlock, 0, (cudaStream_t)stream>>>(p);
+    GS_LAUNCH_CHECK();
+    return GS_OK;
+}
+
+extern "C" int gs_point_bwd_all_points(const float *xyz, const float *features, const int32_t *object_id,
+                                       int64_t n, const gs_view_t *view, int color_max_sh_band,
+                                       float q_factor, float s_factor, float alpha_factor, float color_factor,
+                                       float high_order_color_factor, float *grad_xyz, float *grad_features,
+                                       void *stream)
+{
+    if (n < 0 || !view) return GS_E_INVALID;
+    if (n == 0) return GS_OK;
+    if (!xyz || !features || !object_id || !grad_xyz || !grad_features) return GS_E_INVALID;
+    if (!view->slot_of_point || !view->point_in_camera || !view->splat_grads || !view->intrinsics ||
+        !view->q_cam_pc || !view->t_pc_cam)
+        return GS_E_INVALID;
+    if (((uintptr_t)features | (uintptr_t)grad_features | (uintptr_t)view->splat_grads) & 15u) return GS_E_INVALID;
+    BatchParams p;
+    p.xyz = xyz; p.features = features; p.object_id = object_id;
+    p.first = 0; p.count = n; p.views = nullptr; p.num_views = 1;
+    p.keep = color_max_sh_band <= 0 ? 1 : color_max_sh_band == 1 ? 4 : color_max_sh_band == 2 ? 9 : 16;
+    p.q_factor = q_factor; p.s_factor = s_factor; p.alpha_factor = alpha_factor;
+    p.color_factor = color_factor; p.high_order_color_factor = high_order_color_factor;
+    p.grad_xyz = grad_xyz; p.grad_features = grad_features;
+    p.one = *view;
+    p.inline_one = 1;
+    const long long blocks = (n + kBatchBlock - 1) / kBatchBlock;
     point_bwd_batch_kernel<<<(unsigned)blocks, kBatchBlock, 0, (cudaStream_t)stream>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;

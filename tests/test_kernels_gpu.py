@@ -640,6 +640,33 @@ def test_gradient_batch_equals_per_view_accumulation(n, objects, band):
         _module(hook=lambda h: None).begin_gradient_batch(gx, gf)
 
 
+@pytest.mark.parametrize("n,objects,band", [(5003, 1, 3), (20000, 3, 2)])
+def test_plain_backward_storing_all_rows_equals_zero_fill_plus_scatter(n, objects, band, monkeypatch):
+    """A plain backward (no hook: what the unchanged trainer runs) stores every gradient row with
+    gs_point_bwd_all_points; GS_STORE_ALL_ROWS=0 keeps the reference's shape of the step (zero fill of the
+    N x 59 floats, R.py:1051-1058, then the visible rows).  Same numbers; rows of points the view does not
+    see are exact zeros either way."""
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    scene = make_scene(n, 160, 128, seed=41, scale_factor=0.03, num_objects=objects)
+    g = torch.from_numpy(np.random.default_rng(6).uniform(0, 1, (128, 160, 3)).astype(np.float32)).cuda()
+    grads = {}
+    for store_all in (False, True):
+        monkeypatch.setattr(impl, "STORE_ALL_ROWS", store_all)
+        ras = _module()
+        t = util.scene_tensors(scene, requires_grad=True)
+        image, _, _ = _call(ras, scene, t, band=band)
+        (image * g).sum().backward()
+        torch.cuda.synchronize()
+        grads[store_all] = (t["point_cloud"].grad.clone(), t["point_cloud_features"].grad.clone())
+        assert ras.last_forward_info["num_points_in_camera"] < n
+    for got, want in zip(grads[True], grads[False]):
+        assert torch.isfinite(got).all()
+        l2, mx = util.grad_error(want.cpu().numpy(), got.cpu().numpy())
+        assert l2 <= 1e-6 and mx <= 1e-6, (l2, mx)
+        unseen = (want == 0).all(dim=1)
+        assert bool(unseen.any()) and bool((got[unseen] == 0).all())
+
+
 def test_view_sharded_step_on_two_lanes_matches_one_lane():
     """distributed.ViewShardedTrainerStep with the fused accumulation: six views spread over two CUDA
     streams give the gradient of the one-stream run (up to the order of the RED adds)."""
