@@ -83,6 +83,9 @@ def parse_args():
     ap.add_argument("--exchange-chunks", type=int, default=1,
                     help="N > 1: point ranges the per-point backward of a step is cut into, each all-reduced as "
                          "soon as it is written (1 = one all-reduce after the pass)")
+    ap.add_argument("--c4-assign", default="time", choices=["time", "model"],
+                    help="c4 leg: what the longest-processing-time-first assignment balances -- the measured "
+                         "time of every view alone in the previous pass, or the cost model K + 3 M")
     ap.add_argument("--c4-lanes", type=int, default=8,
                     help="lanes of the c4 leg (its 976x544 views fill the machine less than a 1920x1088 one: "
                          "8 lanes run a rank's 8 views 10 %% faster than 4, tools/exp_c4_rank_step.py)")
@@ -783,17 +786,25 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     rig = Rig(torch, impl, dev, name, lanes, peer_exchange=world > 1 and args.exchange == "fused")
     q_np, t_np = make_views_spread(C4_VIEWS)
     q_dev, t_dev = torch.from_numpy(q_np).to(dev), torch.from_numpy(t_np).to(dev)
-    stats = np.zeros((C4_VIEWS, 2), np.float64)   # per view: M, K of the last recorded pass
+    stats = np.zeros((C4_VIEWS, 3), np.float64)   # per view: M, K, ms alone on one stream (recording pass)
+    view_events = {}
 
     def render_views(mine, record=False):
         def per_view(j, stream):
             v = mine[j]
+            if record:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
             loss = rig.render_loss(q_dev[v:v + 1], t_dev[v:v + 1], rig.wt_dev)
             if record:
+                e1.record()
+                view_events[v] = (e0, e1)
                 info = rig.ras.last_forward_info
-                stats[v] = (float(info["num_points_in_camera"]), float(info["num_keys"]))
+                stats[v, 0:2] = (float(info["num_points_in_camera"]), float(info["num_keys"]))
             return loss
-        return rig.run_views(len(mine), per_view)
+        # the recording pass runs the views one after another on one stream, so that the events around a
+        # view bracket that view's work alone
+        return rig.run_views(len(mine), per_view, use_lanes=not record)
 
     def step(mine, exchange=True):
         rig.begin_step()
@@ -817,17 +828,24 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
     # pass 0 (round robin) measures every view's work; from then on the views are dealt out by
     # longest-processing-time-first on it, the way a trainer would use the previous epoch's numbers
     round_robin = [list(range(r, C4_VIEWS, world)) for r in range(world)]
-    rig.begin_step()
-    render_views(round_robin[rank], record=True)
-    rig.finish_step(dist, 1)
-    torch.cuda.synchronize()
+    for _ in range(2):   # the second pass is the one recorded (allocator and caches warm)
+        view_events.clear()
+        rig.begin_step()
+        render_views(round_robin[rank], record=True)
+        rig.finish_step(dist, 1)
+        torch.cuda.synchronize()
+    for v, (e0, e1) in view_events.items():
+        stats[v, 2] = e0.elapsed_time(e1)
     if world > 1:
         shared = torch.from_numpy(stats).to(dev)
         dist.all_reduce(shared)
         stats = shared.cpu().numpy()
-    m_view, k_view = stats[:, 0], stats[:, 1]
+    m_view, k_view, ms_view = stats[:, 0], stats[:, 1], stats[:, 2]
     from taichi_3d_gaussian_splatting_b200.distributed import assign_views_lpt, view_cost
-    costs = [view_cost(m, k) for m, k in zip(m_view, k_view)]
+    model = [view_cost(m, k) for m, k in zip(m_view, k_view)]
+    # LPT on the MEASURED time of every view (alone, one stream, previous pass): the cost model K + 3 M
+    # correlates 0.8 with it, and the slowest rank is what a step waits for
+    costs = [float(x) for x in ms_view] if args.c4_assign == "time" else model
     assignment, loads = assign_views_lpt(costs, world)
     rr_loads = [sum(costs[v] for v in round_robin[r]) for r in range(world)]
     mine = assignment[rank]
@@ -846,6 +864,8 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         # symmetric buffer of the fused exchange is not one NCCL runs at speed on)
         plain = (torch.zeros(rig.flat.numel(), dtype=torch.float32, device=dev) if rig.peer is not None
                  else rig.flat)
+        for _ in range(3):   # NCCL sets its channels up on the first large calls
+            dist.all_reduce(plain)
         ms_exchange_alone = timed(lambda: dist.all_reduce(plain), 5)
         del plain
         # on-box check of the exchange: the all-reduced gradient of one step against rank 0 rendering all
@@ -874,7 +894,11 @@ def run_c4_leg(torch, dist, impl, dev, rank, world, lanes, args, barrier):
         "exchange": rig.peer_note if world > 1 else "none (one rank)",
         "exchange_error": rig.peer.error() if rig.peer is not None else 0,
         "exchange_ms_alone": ms_exchange_alone, "exchange_ms_alone_what": "NCCL all_reduce of an ordinary buffer of this size", "exchange_bytes": rig.flat.numel() * 4 if world > 1 else 0,
-        "assignment": "longest-processing-time first on K + 3 M of the previous pass",
+        "assignment": ("longest-processing-time first on the measured time of every view alone (previous pass)"
+                       if args.c4_assign == "time" else
+                       "longest-processing-time first on K + 3 M of the previous pass"),
+        "view_ms_alone_min_max": [float(ms_view.min()), float(ms_view.max())],
+        "cost_model_vs_measured_time_correlation": float(np.corrcoef(np.array(model), ms_view)[0, 1]),
         "rank_load_max_over_mean": max(loads) / (sum(loads) / world),
         "rank_load_max_over_mean_round_robin": max(rr_loads) / (sum(rr_loads) / world),
         "views_per_rank": [len(a) for a in assignment],

@@ -1,8 +1,10 @@
 #!/usr/bin/env python
-"""What one rank of the 8-GPU C4 run does between two exchanges, on ONE GPU: a step of 8 of the 64 spread
-views over 2M points (976x544), no exchange.  Sweeps the number of lanes and the order of the views, and
-prints the same views' share of a 64-view step (the no-bubble bound: what the rank's views cost inside a
-long step, where views in flight fill each other's gaps and nothing ramps up or drains).
+"""What the ranks of the 8-GPU C4 run do between two exchanges, emulated on ONE GPU: every rank's share of
+the 64 spread views (2M points, 976x544) run alone as an 8-view step on 8 lanes, for three assignments --
+round robin, longest-processing-time-first on the cost model K + 3 M, and LPT on the MEASURED time of every
+view alone -- beside the per-rank share of a 64-view step (what the views cost inside a long step, where
+nothing ramps up or drains).  (Earlier sweeps with this tool, in profiles/r2_exp_c4_rank_step.json: lanes
+1 / 2 / 4 / 8 and the order of a rank's views; profiles/r2_exp_c4_assignments_one_gpu.json: this output.)
 
     python tools/exp_c4_rank_step.py [--steps 6]
 """
@@ -104,21 +106,6 @@ def main():
         out[f"shares {name}"] = {"max_ms": max(times), "mean_ms": sum(times) / len(times),
                                  "per_rank_ms": [round(x, 2) for x in times]}
     del rig
-    for prio in ():   # (measured: no effect, 51.6 against 51.2 ms for 64 views)
-        impl.PRIORITY_SECTIONS = prio
-        rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", 8)
-        out[f"lanes=8 priority_sections={prio} rank share"] = timed(make_step(rig, mine), args.steps)
-        out[f"lanes=8 priority_sections={prio} 64 views"] = timed(make_step(rig, list(range(bench.C4_VIEWS))), 3)
-        del rig
-    impl.PRIORITY_SECTIONS = False
-    for lanes in ():
-        rig = bench.Rig(torch, impl, dev, "c4_2m_976x544", lanes)
-        orders = {"lpt_order (largest first)": mine,
-                  "smallest_first": list(reversed(mine)),
-                  "interleaved": mine[0::2] + mine[1::2]}
-        for name, order in orders.items():
-            out[f"lanes={lanes} {name}"] = timed(make_step(rig, order), args.steps)
-        del rig
     print(json.dumps(out, indent=1))
 
 
