@@ -86,9 +86,15 @@ __device__ __forceinline__ void batch_block(const BatchParams &p, BatchRows *s_r
     __syncwarp();
     float4 *row = rows + lane * kRowStride4;
 
+    // the slot of the NEXT view is fetched while this view is worked on: an iteration then waits for the
+    // view's 60 bytes only, not for the dependent pair slot -> gradients
+    int slot_next = -1;
+    if (valid && p.num_views > 0) slot_next = __ldg((p.inline_one ? p.one : p.views[0]).slot_of_point + pid);
     for (int v = 0; v < p.num_views; ++v) {
         const gs_view_t &view = p.inline_one ? p.one : p.views[v];
-        const int slot = valid ? __ldg(view.slot_of_point + pid) : -1;
+        const int slot = slot_next;
+        slot_next = -1;
+        if (valid && v + 1 < p.num_views) slot_next = __ldg(p.views[v + 1].slot_of_point + pid);
         if (slot < 0) continue;
         const float4 *sg4 = reinterpret_cast<const float4 *>(view.splat_grads + (size_t)kGradSlots * slot);
         const float4 ga = __ldg(sg4), gb = __ldg(sg4 + 1), gc = __ldg(sg4 + 2);
