@@ -18,6 +18,13 @@ namespace {
 #define GS_PROJ_BLOCK 128
 #endif
 constexpr int kProjBlock = GS_PROJ_BLOCK;
+// GS_PROJ_WALKER: 1 = a fifth warp without points does the CTA's look-back over the preceding blocks, so
+// that the walk runs beside the second half of the four point warps' arithmetic instead of after warp 0's
+#ifndef GS_PROJ_WALKER
+#define GS_PROJ_WALKER 0
+#endif
+constexpr int kProjThreads = kProjBlock + (GS_PROJ_WALKER ? 32 : 0);
+constexpr int kWalkWarp = GS_PROJ_WALKER ? kProjBlock / 32 : 0;
 constexpr unsigned long long kFlagAggregate = 1ull << 62;
 constexpr unsigned long long kFlagPrefix = 2ull << 62;
 constexpr unsigned long long kValueMask = (1ull << 62) - 1;
@@ -139,7 +146,7 @@ __device__ __forceinline__ void mbar_wait(unsigned long long *bar, unsigned pari
 // aligned; the entry point checks).  kOffsets: also produce the exclusive scan of the tile counts
 // (tile_offsets), which only the literal key pipeline reads.
 template <bool kOffsets>
-__global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectParams p)
+__global__ void __launch_bounds__(kProjThreads) project_cull_sh_kernel(ProjectParams p)
 {
     constexpr bool kBulk = true;
     extern __shared__ __align__(128) unsigned char s_dyn[];
@@ -152,10 +159,12 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     if (tid == 0) s_ticket = atomicAdd(p.ticket, 1u);
     __syncthreads();
     const int block = (int)s_ticket;
-    const long long i = (long long)block * kProjBlock + tid;
-    unsigned long long *bar = reinterpret_cast<unsigned long long *>(s_dyn + (size_t)kProjWarps * kWarpRowBytes) + warp;
-    const float4 *s_row = reinterpret_cast<const float4 *>(s_dyn + (size_t)warp * kWarpRowBytes) + 14 * lane;
-    if (kBulk) {
+    const bool walker = GS_PROJ_WALKER && warp == kWalkWarp;   // owns no points: its lanes read as "past the end"
+    const long long i = walker ? p.n + lane : (long long)block * kProjBlock + tid;
+    const int srow = walker ? 0 : warp;
+    unsigned long long *bar = reinterpret_cast<unsigned long long *>(s_dyn + (size_t)kProjWarps * kWarpRowBytes) + srow;
+    const float4 *s_row = reinterpret_cast<const float4 *>(s_dyn + (size_t)srow * kWarpRowBytes) + 14 * lane;
+    if (kBulk && !walker) {
         const long long i0 = i - lane;
         const long long rows = min(32ll, p.n - i0);
         if (lane == 0) {
@@ -286,14 +295,14 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
             unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d);
             if (lane >= d) incl += o;
         }
-        if (lane == 31) s_warp_total[warp] = incl;
+        if (lane == 31 && !walker) s_warp_total[warp] = incl;
     } else {
         // rank among the warp's visible points by ballot; the tiles are only summed
         const unsigned ballot = __ballot_sync(0xffffffffu, visible);
         mine = visible ? 1ull : 0ull;
         incl = (unsigned long long)__popc(ballot & (0xffffffffu >> (31 - lane)));
         const unsigned tiles = __reduce_add_sync(0xffffffffu, (unsigned)count);
-        if (lane == 31) {
+        if (lane == 31 && !walker) {
             s_warp_total[warp] = incl;
             s_warp_tiles[warp] = tiles;
         }
@@ -307,7 +316,7 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
         block_total += t;
         if (!kOffsets) block_tiles += s_warp_tiles[w];
     }
-    if (tid == 0) {
+    if (warp == kWalkWarp && lane == 0) {
         gs_st_volatile_u64(p.status + block, (block == 0 ? kFlagPrefix : kFlagAggregate) | block_total);
         if (!kOffsets && block_tiles) atomicAdd(reinterpret_cast<unsigned long long *>(p.totals) + 1, block_tiles);
     }
@@ -349,7 +358,7 @@ __global__ void __launch_bounds__(kProjBlock) project_cull_sh_kernel(ProjectPara
     }
 
     // ---- ordered compaction, part 2: decoupled look-back over blocks -------------------------
-    if (warp == 0) {
+    if (warp == kWalkWarp) {
         unsigned long long excl = 0;
         if (block > 0) {
             int base = block - 1;
@@ -486,9 +495,9 @@ extern "C" int gs_project_cull_sh(const float *xyz, float *features, const int8_
         attr_set.mark(dev);
     }
     if (offsets)
-        project_cull_sh_kernel<true><<<blocks, kProjBlock, kProjSmem, st>>>(p);
+        project_cull_sh_kernel<true><<<blocks, kProjThreads, kProjSmem, st>>>(p);
     else
-        project_cull_sh_kernel<false><<<blocks, kProjBlock, kProjSmem, st>>>(p);
+        project_cull_sh_kernel<false><<<blocks, kProjThreads, kProjSmem, st>>>(p);
     GS_LAUNCH_CHECK();
     return GS_OK;
 }
