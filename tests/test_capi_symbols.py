@@ -43,3 +43,41 @@ def test_library_is_sm100a_only():
     out = subprocess.run([cuobjdump, "-lelf", _capi.LIB_PATH], capture_output=True, text=True).stdout
     archs = set(re.findall(r"sm_\d+a?", out))
     assert archs == {"sm_100a"}, archs
+
+
+def test_struct_layouts_match_the_header():
+    """gs_view_t and gs_exchange_t as ctypes declares them have the size and field offsets the C compiler
+    gives the header's structs (they cross the ABI by pointer / by value in kernel arguments)."""
+    import subprocess
+    import tempfile
+    from taichi_3d_gaussian_splatting_b200 import _capi
+    fields = {"gs_view_t": ["slot_of_point", "point_in_camera", "splat_grads", "intrinsics", "q_cam_pc",
+                            "t_pc_cam", "reserved"],
+              "gs_exchange_t": ["multicast_base", "local_base", "flags", "rank", "world", "chunks",
+                                "reducer_ctas", "epoch", "reserved", "scratch"]}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "gs_b200.h"', 'int main(void) {']
+    for name, fs in fields.items():
+        lines.append(f'printf("{name} %zu", sizeof({name}));')
+        for f in fs:
+            lines.append(f'printf(" %zu", offsetof({name}, {f}));')
+        lines.append('printf("\\n");')
+    lines += ['return 0;', '}']
+    with tempfile.TemporaryDirectory() as tmp:
+        src, exe = os.path.join(tmp, "layout.c"), os.path.join(tmp, "layout")
+        open(src, "w").write("\n".join(lines))
+        subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), src, "-o", exe], check=True)
+        out = subprocess.run([exe], capture_output=True, text=True, check=True).stdout.split("\n")
+    for line in out:
+        if not line.strip():
+            continue
+        name, size, *offsets = line.split()
+        ct = getattr(_capi, name)
+        assert ctypes.sizeof(ct) == int(size), name
+        assert [getattr(ct, f).offset for f in fields[name]] == [int(o) for o in offsets], name
+
+
+def test_exchange_sizes_without_a_gpu():
+    from taichi_3d_gaussian_splatting_b200 import _capi
+    assert _capi.lib.gs_exchange_flag_words(4, 8) == 2 * 4 * 8
+    assert _capi.lib.gs_exchange_scratch_bytes(4) == 4 * (2 + 2 * 4)
+    assert _capi.lib.gs_exchange_flag_words(0, 8) < 0 and _capi.lib.gs_exchange_scratch_bytes(0) < 0
