@@ -111,3 +111,37 @@ def test_product_package_never_imports_the_oracle():
                 text = open(os.path.join(dirpath, f)).read()
                 assert not re.search(r"^\s*(from|import)\s+oracle|gs_oracle\.(py|so)|libgs_oracle",
                                      text, flags=re.M), f
+
+
+def test_gradient_batch_api_rejects_misuse_on_the_host():
+    """begin_gradient_batch / end_gradient_batch / accumulate_gradients_into validate before anything
+    is launched: CPU buffers, wrong shapes, a hook, a missing begin."""
+    import pytest
+    import taichi_3d_gaussian_splatting_b200.GaussianPointCloudRasterisation as impl
+    Ras = impl.GaussianPointCloudRasterisation
+    ras = Ras(Ras.GaussianPointCloudRasterisationConfig())
+    gx, gf = torch.zeros(8, 3), torch.zeros(8, 56)
+    with pytest.raises(ValueError):
+        ras.accumulate_gradients_into(gx, gf)          # CPU tensors: there is no CPU path
+    with pytest.raises(ValueError):
+        ras.begin_gradient_batch(gx, gf)
+    with pytest.raises(RuntimeError):
+        ras.end_gradient_batch()                        # nothing was begun
+    hooked = Ras(Ras.GaussianPointCloudRasterisationConfig(), backward_valid_point_hook=lambda h: None)
+    with pytest.raises(ValueError, match="hook"):
+        hooked.begin_gradient_batch(gx, gf)
+    ras.accumulate_gradients_into(None, None)           # restoring the reference behaviour always works
+    assert ras._accumulate_into is None and ras._batch is None
+
+
+def test_views_and_lpt_assignment_cover_every_view_once():
+    from taichi_3d_gaussian_splatting_b200.distributed import assign_views_lpt, view_cost, views_of_rank
+    costs = [view_cost(m, k) for m, k in ((1.0e6, 9.0e6), (0.6e6, 4.4e6), (1.9e6, 9.9e6), (1.2e6, 7.0e6),
+                                            (0.9e6, 5.0e6))]
+    for world in (1, 2, 3, 5, 8):
+        mine, loads = assign_views_lpt(costs, world)
+        assert sorted(v for share in mine for v in share) == list(range(len(costs)))
+        assert abs(sum(loads) - sum(costs)) < 1e-6 * sum(costs)
+        if world <= len(costs):
+            assert all(share for share in mine)          # >= world views: nobody is left without one
+        assert sorted(v for r in range(world) for v in views_of_rank(len(costs), r, world)) == list(range(len(costs)))
