@@ -3,7 +3,7 @@
 same calls on a cloud so small that the GPU work is negligible, so the wall time per view is what the host
 needs to enqueue a view (Python, allocator, launches, the {M, K} read-back round trip).
 
-    python tools/exp_host_overhead.py [--views 64] [--lanes 4]
+    python tools/exp_host_overhead.py [--views 64]      # lanes 1, 4 and 8 are all measured
 """
 import argparse
 import json
